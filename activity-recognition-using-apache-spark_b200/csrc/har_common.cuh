@@ -1,0 +1,112 @@
+// Shared host/device helpers for the sm_100a kernels behind include/har_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/har_b200.h"
+
+#define HAR_API extern "C" __attribute__((visibility("default")))
+
+namespace har {
+
+constexpr int kNumSMs = 148;          // B200: 2 dies x 74 SMs
+
+std::string& last_error();
+int fail(int code, const char* fmt, ...);
+void count_launch(int n = 1);
+long long launches_since_reset();
+void reset_launches();
+
+// optional CUDA-event timing of selected kernels (har_debug_profile_*; off by default)
+enum ProfId { PROF_NODE_HIST = 0, PROF_BEST_SPLIT, PROF_PART_COUNT, PROF_PART_SCATTER, PROF_WINDOW_FEATURES,
+              PROF_SEG_TILES, PROF_PREDICT, PROF_BIN, PROF_FIND_SPLITS, PROF_BAG, PROF_NUM };
+bool prof_enabled();
+void prof_begin(cudaStream_t s);
+void prof_end(int id, cudaStream_t s, double units);
+void prof_resolve();
+
+#define HAR_CUDA(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess)                                                                 \
+            return har::fail(HAR_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                             __FILE__, __LINE__);                                              \
+    } while (0)
+
+#define HAR_LAUNCH_CHECK()                                                                     \
+    do {                                                                                       \
+        har::count_launch();                                                                   \
+        cudaError_t _e = cudaGetLastError();                                                   \
+        if (_e != cudaSuccess)                                                                 \
+            return har::fail(HAR_E_CUDA, "kernel launch failed: %s (%s:%d)",                   \
+                             cudaGetErrorString(_e), __FILE__, __LINE__);                      \
+    } while (0)
+
+// Stream-ordered scratch buffer (cudaMallocAsync); freed on the same stream.
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaStream_t s = nullptr;
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    ~DevBuf() { release(); }
+    cudaError_t alloc(size_t count, cudaStream_t stream) {
+        release();
+        s = stream;
+        n = count;
+        if (count == 0) return cudaSuccess;
+        return cudaMallocAsync((void**)&p, count * sizeof(T), stream);
+    }
+    void release() {
+        if (p) cudaFreeAsync(p, s);
+        p = nullptr;
+        n = 0;
+    }
+};
+
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// java.lang.Double.compare total order as a sortable unsigned key (NaN canonical, greatest).
+__host__ __device__ inline uint64_t jd_key(double x) {
+    if (x != x) return 0xfff8000000000000ULL;
+#ifdef __CUDA_ARCH__
+    uint64_t b = (uint64_t)__double_as_longlong(x);
+#else
+    uint64_t b;
+    memcpy(&b, &x, 8);
+#endif
+    return (b & 0x8000000000000000ULL) ? ~b : (b | 0x8000000000000000ULL);
+}
+__host__ __device__ inline double jd_unkey(uint64_t k) {
+    uint64_t b = (k & 0x8000000000000000ULL) ? (k & 0x7fffffffffffffffULL) : ~k;
+#ifdef __CUDA_ARCH__
+    return __longlong_as_double((long long)b);
+#else
+    double x;
+    memcpy(&x, &b, 8);
+    return x;
+#endif
+}
+
+// java.util.Arrays.binarySearch(double[], key) + `if (idx >= 0) idx else -idx - 1` (TreePoint.findBin)
+__host__ __device__ inline int java_find_bin(const double* thr, int n, double key) {
+    uint64_t kk = jd_key(key);
+    int low = 0, high = n - 1;
+    while (low <= high) {
+        int mid = (low + high) >> 1;
+        uint64_t mk = jd_key(thr[mid]);
+        if (mk < kk) low = mid + 1;
+        else if (mk > kk) high = mid - 1;
+        else return mid;
+    }
+    return low;
+}
+
+}  // namespace har

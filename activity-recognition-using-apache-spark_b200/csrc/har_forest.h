@@ -1,0 +1,25 @@
+// The opaque har_forest handle: flat host copy of the (pruned) trees + lazily built device tables.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+struct har_forest {
+    int T = 0, C = 0, F = 0;
+    // flat, pre-order per tree (see har_forest_export in include/har_b200.h)
+    std::vector<int64_t> tree_off;
+    std::vector<int32_t> feature, left, right, node_id, arity;
+    std::vector<double> threshold, prediction, impurity, gain, stats;
+    std::vector<uint64_t> left_mask;
+    // fit by-products
+    std::vector<double> thresholds;
+    std::vector<int32_t> nsplits;
+    int max_bins = 0;
+    int64_t num_groups = 0, num_batches = 0, num_launches = 0;
+    // device tables for predict (built on first use, on the device current at that time)
+    int dev = -1;
+    void* d_nodes = nullptr;      // PNode[total]
+    double* d_leaf = nullptr;     // [num_leaves][C]: DT = class counts, RF = counts / total
+    int64_t* d_roots = nullptr;   // [T] index of each tree's root in d_nodes
+    int leaf_mode = -1;           // is_forest flag the leaf table was built for
+    int max_depth = 0;
+};

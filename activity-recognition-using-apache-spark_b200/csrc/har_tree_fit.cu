@@ -1,0 +1,776 @@
+// Host driver of the MLlib-compatible tree trainer + the stage-level entry points of
+// include/har_b200.h (har_find_splits, har_bin_features, har_bag_weights, har_node_histogram,
+// har_forest_fit, har_forest_export ...).
+//
+// Stands in for ml.tree.impl.RandomForest.run, reached from Main/main.py:300 (`dt.fit(train)`) and
+// :481 (`rf.fit(train)`).  The driver-side control flow (node stack, selectNodesToSplit memory-bounded
+// groups, feature-subset draws, child creation, pruning) follows SURVEY.md A.5-A.9 on the host, as it
+// does on Spark's driver; everything that touches rows runs in the kernels of har_tree_kernels.cuh.
+#include <algorithm>
+#include <cmath>
+#include <memory>
+
+#include "har_forest.h"
+#include "har_tree_kernels.cuh"
+
+using namespace har;
+
+namespace {
+
+// ---- DecisionTreeMetadata.buildMetadata -------------------------------------------
+struct Meta {
+    int F = 0, C = 0, mpb = 0;
+    std::vector<int32_t> arity, num_bins, num_splits, hist_bins;
+    std::vector<uint8_t> kind;
+    std::vector<int32_t> loff;     // [F+1] word offsets of the full-width node histogram
+};
+
+int build_meta(Meta& m, int F, int C, int64_t n_global, int max_bins, const int32_t* arity) {
+    m.F = F; m.C = C;
+    m.mpb = (int)std::min<int64_t>(max_bins, n_global);
+    m.arity.assign(F, 0); m.num_bins.assign(F, 0); m.num_splits.assign(F, 0); m.hist_bins.assign(F, 0);
+    m.kind.assign(F, KIND_CONT);
+    const int max_unordered = (int)std::floor(std::log((double)(m.mpb / 2 + 1)) / std::log(2.0) + 1.0);
+    for (int f = 0; f < F; f++) {
+        int k = arity ? arity[f] : 0;
+        if (k <= 1) k = 0;
+        m.arity[f] = k;
+        if (k > m.mpb)
+            return fail(HAR_E_INVALID,
+                        "DecisionTree requires maxBins (= %d) to be at least as large as the number of values in each "
+                        "categorical feature, but categorical feature %d has %d values. Considering remove this and "
+                        "other categorical features with a large number of values, or add more training examples.",
+                        m.mpb, f, k);
+        if (k > MAX_CAT)
+            return fail(HAR_E_UNSUPPORTED, "categorical feature %d has %d values; this library supports at most %d", f, k, MAX_CAT);
+        if (k == 0) { m.num_bins[f] = m.mpb; m.num_splits[f] = m.mpb - 1; }
+        else if (C > 2 && k <= max_unordered) { m.kind[f] = KIND_UNORDERED; m.num_bins[f] = (1 << (k - 1)) - 1; m.num_splits[f] = m.num_bins[f]; }
+        else { m.kind[f] = KIND_ORDERED; m.num_bins[f] = k; m.num_splits[f] = k - 1; }
+    }
+    return HAR_OK;
+}
+
+int finish_meta(Meta& m) {
+    m.loff.assign(m.F + 1, 0);
+    int64_t off = 0;
+    for (int f = 0; f < m.F; f++) {
+        m.hist_bins[f] = m.arity[f] ? m.arity[f] : m.num_bins[f];
+        m.loff[f] = (int32_t)off;
+        off += (int64_t)m.hist_bins[f] * m.C;
+        if (off > 0x7fffffff) return fail(HAR_E_UNSUPPORTED, "node histogram exceeds 2^31 counters");
+    }
+    m.loff[m.F] = (int32_t)off;
+    return HAR_OK;
+}
+
+int dist_allreduce(const har_dist* d, void* buf, int64_t count, cudaStream_t s) {
+    if (!d || d->world_size <= 1 || count == 0) return HAR_OK;
+    if (!d->allreduce_i32) return fail(HAR_E_INVALID, "har_dist.allreduce_i32 is NULL with world_size > 1");
+    int rc = d->allreduce_i32(d->ctx, buf, count, (har_stream_t)s);
+    if (rc != 0) return fail(HAR_E_COMM, "all-reduce callback failed with code %d", rc);
+    return HAR_OK;
+}
+
+// ---- RandomForest.findSplits row sample (RDD.sample -> BernoulliSampler / GapSampling) -----------
+void sample_rows(int64_t n_global, int mpb, int64_t seed, const int64_t* part_off, int num_parts,
+                 int partition_offset, std::vector<int64_t>& out) {
+    int64_t required = std::max<int64_t>((int64_t)mpb * mpb, 10000);
+    out.clear();
+    if (required >= n_global) {
+        for (int64_t i = part_off[0]; i < part_off[num_parts]; i++) out.push_back(i);
+        return;
+    }
+    const double fraction = (double)required / (double)n_global;
+    XorShift sx(seed);
+    JavaRand jr((int64_t)sx.next_int());
+    for (int p = 0; p < partition_offset; p++) jr.next_long();
+    for (int p = 0; p < num_parts; p++) {
+        XorShift rng(jr.next_long());
+        if (fraction <= 0.4) {
+            const double lnq = std::log1p(-fraction);
+            auto advance = [&]() { double u = std::max(rng.next_double(), 5e-11); return (int)(std::log(u) / lnq); };
+            int drop = advance();
+            for (int64_t i = part_off[p]; i < part_off[p + 1]; i++) {
+                if (drop > 0) { drop--; continue; }
+                drop = advance();
+                out.push_back(i);
+            }
+        } else {
+            for (int64_t i = part_off[p]; i < part_off[p + 1]; i++)
+                if (rng.next_double() <= fraction) out.push_back(i);
+        }
+    }
+}
+
+int find_splits_impl(const double* d_X, int64_t n, int F, int64_t ld, const Meta& m, int max_bins, int64_t seed,
+                     const int64_t* part_off, int num_parts, const har_dist* dist, double* thresholds,
+                     int32_t* nsplits, cudaStream_t s) {
+    std::fill(thresholds, thresholds + (size_t)F * max_bins, 0.0);
+    std::fill(nsplits, nsplits + F, 0);
+    std::vector<int32_t> cont;
+    for (int f = 0; f < F; f++) if (m.arity[f] == 0) cont.push_back(f);
+    const int nfc = (int)cont.size();
+    if (nfc == 0) return HAR_OK;
+    const int64_t n_global = dist ? dist->global_rows : n;
+    const int world = dist ? dist->world_size : 1, rank = dist ? dist->rank : 0;
+    std::vector<int64_t> rows;
+    sample_rows(n_global, m.mpb, seed, part_off, num_parts, dist ? dist->partition_offset : 0, rows);
+    const int64_t ns_local = (int64_t)rows.size();
+    int64_t col0 = 0, ns_total = ns_local;
+    if (world > 1) {
+        DevBuf<int32_t> cnt;
+        HAR_CUDA(cnt.alloc(world, s));
+        HAR_CUDA(cudaMemsetAsync(cnt.p, 0, sizeof(int32_t) * world, s));
+        int32_t mine = (int32_t)ns_local;
+        HAR_CUDA(cudaMemcpyAsync(cnt.p + rank, &mine, sizeof(int32_t), cudaMemcpyHostToDevice, s));
+        if (int rc = dist_allreduce(dist, cnt.p, world, s)) return rc;
+        std::vector<int32_t> all(world);
+        HAR_CUDA(cudaMemcpyAsync(all.data(), cnt.p, sizeof(int32_t) * world, cudaMemcpyDeviceToHost, s));
+        HAR_CUDA(cudaStreamSynchronize(s));
+        ns_total = 0;
+        for (int r = 0; r < world; r++) { if (r == rank) col0 = ns_total; ns_total += all[r]; }
+    }
+    if (ns_total == 0) return HAR_OK;
+    DevBuf<double> S, thr;
+    DevBuf<int64_t> d_rows;
+    DevBuf<int32_t> d_cont, d_ns;
+    DevBuf<uint64_t> scratch;
+    HAR_CUDA(S.alloc((size_t)nfc * ns_total, s));
+    HAR_CUDA(d_rows.alloc(std::max<int64_t>(ns_local, 1), s));
+    HAR_CUDA(d_cont.alloc(nfc, s)); HAR_CUDA(d_ns.alloc(nfc, s)); HAR_CUDA(thr.alloc((size_t)nfc * max_bins, s));
+    if (world > 1) HAR_CUDA(cudaMemsetAsync(S.p, 0, sizeof(double) * nfc * ns_total, s));
+    HAR_CUDA(cudaMemcpyAsync(d_cont.p, cont.data(), sizeof(int32_t) * nfc, cudaMemcpyHostToDevice, s));
+    if (ns_local) {
+        HAR_CUDA(cudaMemcpyAsync(d_rows.p, rows.data(), sizeof(int64_t) * ns_local, cudaMemcpyHostToDevice, s));
+        k_gather_sample<<<(unsigned)ceil_div(ns_local * nfc, 256), 256, 0, s>>>(d_X, ld, d_rows.p, ns_local, d_cont.p, nfc,
+                                                                                S.p, ns_total, col0);
+        HAR_LAUNCH_CHECK();
+    }
+    // all-gather of the sample as an integer all-reduce: every slot is non-zero on exactly one rank
+    if (int rc = dist_allreduce(dist, S.p, (int64_t)nfc * ns_total * 2, s)) return rc;
+    int64_t npad = 2;
+    while (npad < ns_total) npad <<= 1;
+    size_t smem = 0;
+    if (npad <= 16384) smem = (size_t)npad * sizeof(uint64_t);
+    else HAR_CUDA(scratch.alloc((size_t)nfc * npad, s));
+    HAR_CUDA(cudaMemsetAsync(thr.p, 0, sizeof(double) * nfc * max_bins, s));
+    HAR_CUDA(cudaFuncSetAttribute(k_find_splits, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 * 8));
+    prof_begin(s);
+    k_find_splits<<<nfc, 512, smem, s>>>(S.p, ns_total, npad, m.mpb - 1, max_bins, scratch.p, thr.p, d_ns.p);
+    HAR_LAUNCH_CHECK();
+    prof_end(PROF_FIND_SPLITS, s, (double)ns_total);
+    std::vector<double> h_thr((size_t)nfc * max_bins);
+    std::vector<int32_t> h_ns(nfc);
+    HAR_CUDA(cudaMemcpyAsync(h_thr.data(), thr.p, sizeof(double) * nfc * max_bins, cudaMemcpyDeviceToHost, s));
+    HAR_CUDA(cudaMemcpyAsync(h_ns.data(), d_ns.p, sizeof(int32_t) * nfc, cudaMemcpyDeviceToHost, s));
+    HAR_CUDA(cudaStreamSynchronize(s));
+    for (int j = 0; j < nfc; j++) {
+        nsplits[cont[j]] = h_ns[j];
+        std::copy(h_thr.begin() + (size_t)j * max_bins, h_thr.begin() + (size_t)(j + 1) * max_bins,
+                  thresholds + (size_t)cont[j] * max_bins);
+    }
+    return HAR_OK;
+}
+
+int bin_features_impl(const double* d_X, int64_t n, int F, int64_t ld, const int32_t* arity, const double* thresholds,
+                      const int32_t* nsplits, int max_bins, uint8_t* d_bins, int64_t ldb, cudaStream_t s) {
+    if (n == 0) return HAR_OK;
+    DevBuf<int32_t> d_ar, d_ns;
+    DevBuf<double> d_thr;
+    DevBuf<unsigned long long> bad;
+    HAR_CUDA(d_ar.alloc(F, s)); HAR_CUDA(d_ns.alloc(F, s)); HAR_CUDA(d_thr.alloc((size_t)F * max_bins, s));
+    HAR_CUDA(bad.alloc(1, s));
+    std::vector<int32_t> ar(F, 0);
+    if (arity) std::copy(arity, arity + F, ar.begin());
+    HAR_CUDA(cudaMemcpyAsync(d_ar.p, ar.data(), sizeof(int32_t) * F, cudaMemcpyHostToDevice, s));
+    HAR_CUDA(cudaMemcpyAsync(d_ns.p, nsplits, sizeof(int32_t) * F, cudaMemcpyHostToDevice, s));
+    HAR_CUDA(cudaMemcpyAsync(d_thr.p, thresholds, sizeof(double) * F * max_bins, cudaMemcpyHostToDevice, s));
+    HAR_CUDA(cudaMemsetAsync(bad.p, 0xff, sizeof(unsigned long long), s));
+    int64_t blocks = std::min<int64_t>(ceil_div(n * F, 256), (int64_t)kNumSMs * 32);
+    prof_begin(s);
+    k_bin_features<<<(unsigned)blocks, 256, 0, s>>>(d_X, n, F, ld, d_ar.p, d_thr.p, d_ns.p, max_bins, d_bins, ldb, bad.p);
+    HAR_LAUNCH_CHECK();
+    prof_end(PROF_BIN, s, (double)n);
+    unsigned long long h_bad = 0;
+    HAR_CUDA(cudaMemcpyAsync(&h_bad, bad.p, sizeof h_bad, cudaMemcpyDeviceToHost, s));
+    HAR_CUDA(cudaStreamSynchronize(s));
+    if (h_bad != ~0ULL) {
+        int64_t i = (int64_t)(h_bad / F);
+        int f = (int)(h_bad % F);
+        double v = 0;
+        cudaMemcpy(&v, d_X + i * ld + f, sizeof(double), cudaMemcpyDeviceToHost);
+        return fail(HAR_E_INVALID,
+                    "DecisionTree given invalid data: Feature %d is categorical with values in {0,...,%d}, but a data "
+                    "point gives it value %g.\n  Bad data point: row %lld", f, ar[f] - 1, v, (long long)i);
+    }
+    return HAR_OK;
+}
+
+int bag_weights_impl(int64_t n, int T, double rate, int64_t seed, const int64_t* part_off, int num_parts,
+                     int partition_offset, uint8_t* d_w, cudaStream_t s) {
+    if (n == 0) return HAR_OK;
+    if (T == 1 && rate == 1.0) { HAR_CUDA(cudaMemsetAsync(d_w, 1, (size_t)n, s)); return HAR_OK; }
+    DevBuf<int64_t> d_po;
+    HAR_CUDA(d_po.alloc(num_parts + 1, s));
+    HAR_CUDA(cudaMemcpyAsync(d_po.p, part_off, sizeof(int64_t) * (num_parts + 1), cudaMemcpyHostToDevice, s));
+    prof_begin(s);
+    k_bag_weights<<<(unsigned)ceil_div(num_parts, 32), 32, 0, s>>>(n, T, rate, std::exp(-rate), seed, d_po.p, num_parts,
+                                                                   partition_offset, T > 1 ? 1 : 0, d_w);
+    HAR_LAUNCH_CHECK();
+    prof_end(PROF_BAG, s, (double)n * T);
+    HAR_CUDA(cudaStreamSynchronize(s));       // part_off is a caller buffer
+    return HAR_OK;
+}
+
+// ---- Scala 2.11 mutable.HashMap[Int, _] iteration order (findBestSplits' nodesForGroup.foreach) ----
+uint32_t bswap32(uint32_t x) { return (x >> 24) | ((x >> 8) & 0xff00u) | ((x << 8) & 0xff0000u) | (x << 24); }
+int scala_index(uint32_t hcode, int table_len) {
+    uint32_t i = bswap32(hcode * 0x9e3775cdu) * 0x9e3775cdu;
+    uint32_t rotated = (i >> 4) | (i << 28);                 // seedvalue = bitCount(initial table length - 1) = 4
+    int ones = table_len - 1;
+    return (int)((rotated >> __builtin_clz((unsigned)ones)) & (uint32_t)ones);
+}
+std::vector<int> scala_hashmap_order(const std::vector<int>& keys) {
+    int tlen = 16, thr = 12, size = 0;
+    std::vector<int> head(tlen, -1), next(keys.size(), -1);
+    for (int k = 0; k < (int)keys.size(); k++) {
+        int h = scala_index((uint32_t)keys[k], tlen);
+        next[k] = head[h]; head[h] = k;
+        if (++size > thr) {
+            int nlen = tlen * 2;
+            std::vector<int> nh(nlen, -1);
+            for (int i = tlen - 1; i >= 0; i--)
+                for (int e = head[i]; e >= 0;) {
+                    int e1 = next[e];
+                    int hh = scala_index((uint32_t)keys[e], nlen);
+                    next[e] = nh[hh]; nh[hh] = e;
+                    e = e1;
+                }
+            head.swap(nh); tlen = nlen; thr = (int)((int64_t)nlen * 750 / 1000);
+        }
+    }
+    std::vector<int> out;
+    for (int i = tlen - 1; i >= 0; i--) for (int e = head[i]; e >= 0; e = next[e]) out.push_back(e);
+    return out;
+}
+
+// SamplingUtils.reservoirSampleAndCount(0 until F, k, seed)  
+void reservoir_features(int F, int k, int64_t seed, int32_t* out) {
+    int i = 0;
+    for (; i < k && i < F; i++) out[i] = i;
+    if (i < k) return;
+    int64_t l = i;
+    XorShift r(seed);
+    for (int item = i; item < F; item++) {
+        l++;
+        int64_t j = (int64_t)(r.next_double() * (double)l);
+        if (j < k) out[j] = item;
+    }
+}
+
+// ---- LearningNode ---------------------------------------------------------------------------------
+struct LNode {
+    int32_t id = 1;
+    bool is_leaf = false, valid = true;
+    int feature = -1, kind = 0, split = 0, arity = 0;
+    double threshold = 0, gain = 0, impurity = 0;
+    uint64_t mask = 0;
+    std::vector<double> stats;
+    int left = -1, right = -1;
+    // rows of this rank at the node
+    int64_t start = 0;
+    int32_t count = 0;
+    int buf = 0;
+    std::vector<int32_t> subset;
+};
+int level_of(int id) { int l = 0; while (id > 1) { id >>= 1; l++; } return l; }
+int first_argmax(const double* s, int C) {
+    int b = -1; double mv = 0;
+    for (int c = 0; c < C; c++) if (b < 0 || s[c] > mv) { b = c; mv = s[c]; }
+    return b;
+}
+
+// LearningNode.toNode(prune = true) into the flat pre-order layout
+int64_t emit_node(har_forest& fo, const std::vector<LNode>& tree, int idx, int64_t base, bool* is_leaf_out) {
+    const LNode& n = tree[idx];
+    const int C = fo.C;
+    const int64_t me = (int64_t)fo.feature.size();
+    fo.feature.push_back(-1); fo.left.push_back(-1); fo.right.push_back(-1); fo.node_id.push_back(n.id);
+    fo.arity.push_back(0); fo.threshold.push_back(0.0); fo.left_mask.push_back(0);
+    fo.prediction.push_back((double)first_argmax(n.stats.data(), C));
+    fo.impurity.push_back(0.0); fo.gain.push_back(0.0);
+    fo.stats.insert(fo.stats.end(), n.stats.begin(), n.stats.end());
+    if (n.left >= 0) {
+        bool ll = false, rl = false;
+        int64_t li = emit_node(fo, tree, n.left, base, &ll);
+        int64_t ri = emit_node(fo, tree, n.right, base, &rl);
+        if (ll && rl && fo.prediction[base + li] == fo.prediction[base + ri]) {
+            const size_t keep = (size_t)me + 1;
+            fo.feature.resize(keep); fo.left.resize(keep); fo.right.resize(keep); fo.node_id.resize(keep);
+            fo.arity.resize(keep); fo.threshold.resize(keep); fo.left_mask.resize(keep); fo.prediction.resize(keep);
+            fo.impurity.resize(keep); fo.gain.resize(keep); fo.stats.resize(keep * C);
+            fo.impurity[me] = n.impurity;
+            *is_leaf_out = true;
+            return me - base;
+        }
+        fo.feature[me] = n.feature; fo.left[me] = (int32_t)li; fo.right[me] = (int32_t)ri;
+        fo.arity[me] = n.kind ? n.arity : 0;
+        fo.threshold[me] = n.threshold; fo.left_mask[me] = n.mask; fo.gain[me] = n.gain; fo.impurity[me] = n.impurity;
+        *is_leaf_out = false;
+        return me - base;
+    }
+    fo.impurity[me] = n.valid ? n.impurity : -1.0;
+    *is_leaf_out = true;
+    return me - base;
+}
+
+template <typename T>
+struct Pinned {
+    T* p = nullptr;
+    size_t cap = 0;
+    ~Pinned() { if (p) cudaFreeHost(p); }
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = std::max(n, cap * 2);
+        return cudaMallocHost((void**)&p, cap * sizeof(T));
+    }
+};
+
+struct GroupItem { int tree; int node; };
+
+}  // namespace
+
+// =====================================================================================================
+HAR_API int har_find_splits(const double* d_X, int64_t n, int32_t F, int64_t ld, const int32_t* arity, int32_t max_bins,
+                            int64_t seed, const int64_t* part_off, int32_t num_parts, const har_dist* dist,
+                            double* thresholds, int32_t* nsplits, har_stream_t stream) {
+    if (F <= 0 || max_bins < 2 || max_bins > HAR_MAX_BINS) return fail(HAR_E_INVALID, "har_find_splits: bad F / max_bins");
+    Meta m;
+    if (int rc = build_meta(m, F, 3, dist ? dist->global_rows : n, max_bins, arity)) return rc;
+    int64_t po[2] = {0, n};
+    if (!part_off) { part_off = po; num_parts = 1; }
+    return find_splits_impl(d_X, n, F, ld, m, max_bins, seed, part_off, num_parts, dist, thresholds, nsplits, (cudaStream_t)stream);
+}
+
+HAR_API int har_bin_features(const double* d_X, int64_t n, int32_t F, int64_t ld, const int32_t* arity,
+                             const double* thresholds, const int32_t* nsplits, int32_t max_bins, uint8_t* d_bins,
+                             int64_t ldb, har_stream_t stream) {
+    if (F <= 0 || ldb < F) return fail(HAR_E_INVALID, "har_bin_features: need ldb >= num_features");
+    return bin_features_impl(d_X, n, F, ld, arity, thresholds, nsplits, max_bins, d_bins, ldb, (cudaStream_t)stream);
+}
+
+HAR_API int har_bag_weights(int64_t n, int32_t T, double rate, int64_t seed, const int64_t* part_off, int32_t num_parts,
+                            int32_t partition_offset, uint8_t* d_weights, har_stream_t stream) {
+    if (T < 1 || !(rate > 0.0) || rate > 1.0) return fail(HAR_E_INVALID, "har_bag_weights: need num_trees >= 1 and rate in (0, 1]");
+    int64_t po[2] = {0, n};
+    if (!part_off) { part_off = po; num_parts = 1; }
+    return bag_weights_impl(n, T, rate, seed, part_off, num_parts, partition_offset, d_weights, (cudaStream_t)stream);
+}
+
+HAR_API int har_node_histogram(const uint8_t* d_bins, int64_t ldb, const uint8_t* d_labels, const uint8_t* d_weights,
+                               const int32_t* d_rows, int64_t nrows, int32_t F, int32_t C, const int64_t* hist_off,
+                               uint32_t* d_hist, uint32_t* d_parent, har_stream_t stream) {
+    if (C < 1 || C > HAR_MAX_CLASSES) return fail(HAR_E_UNSUPPORTED, "num_classes must be in [1, %d]", HAR_MAX_CLASSES);
+    if (nrows <= 0) return HAR_OK;
+    if (nrows > 0x7fffffff || hist_off[F] > 0x7fffffff) return fail(HAR_E_UNSUPPORTED, "har_node_histogram: sizes exceed 2^31");
+    cudaStream_t s = (cudaStream_t)stream;
+    std::vector<int32_t> loff(F + 1);
+    for (int f = 0; f <= F; f++) loff[f] = (int32_t)hist_off[f];
+    for (int f = 0; f < F; f++)
+        if ((int64_t)(loff[f + 1] - loff[f]) > HIST_TILE_WORDS)
+            return fail(HAR_E_UNSUPPORTED, "feature %d needs %d counters; tile limit is %d", f, loff[f + 1] - loff[f], HIST_TILE_WORDS);
+    const int chunk_rows = 2048;
+    NodeDesc nd{};
+    nd.start = 0; nd.hist_base = 0; nd.count = (int32_t)nrows; nd.tree = 0; nd.buf = 0; nd.level = 0; nd.sub_off = 0;
+    nd.nf = F; nd.hist_len = loff[F];
+    int32_t item_off[2] = {0, (int32_t)ceil_div(nrows, chunk_rows)};
+    DevBuf<NodeDesc> d_nd; DevBuf<int32_t> d_io, d_loff; DevBuf<uint8_t> d_kind;
+    HAR_CUDA(d_nd.alloc(1, s)); HAR_CUDA(d_io.alloc(2, s)); HAR_CUDA(d_loff.alloc(F + 1, s)); HAR_CUDA(d_kind.alloc(F, s));
+    HAR_CUDA(cudaMemcpyAsync(d_nd.p, &nd, sizeof nd, cudaMemcpyHostToDevice, s));
+    HAR_CUDA(cudaMemcpyAsync(d_io.p, item_off, sizeof item_off, cudaMemcpyHostToDevice, s));
+    HAR_CUDA(cudaMemcpyAsync(d_loff.p, loff.data(), sizeof(int32_t) * (F + 1), cudaMemcpyHostToDevice, s));
+    HAR_CUDA(cudaMemsetAsync(d_kind.p, KIND_CONT, F, s));
+    const size_t smem = (HIST_TILE_WORDS + 32) * sizeof(uint32_t);
+    const bool vec = (ldb % 16 == 0) && ((reinterpret_cast<uintptr_t>(d_bins) & 15) == 0);
+    if (vec) {
+        HAR_CUDA(cudaFuncSetAttribute(k_node_hist<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_node_hist<false><<<item_off[1], HIST_THREADS, smem, s>>>(d_nd.p, d_io.p, 1, chunk_rows, d_bins, ldb, d_labels, d_weights,
+                                                                  nrows, d_rows, nullptr, nullptr, d_loff.p, d_kind.p, C, d_hist, d_parent);
+    } else {
+        HAR_CUDA(cudaFuncSetAttribute(k_node_hist<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_node_hist<true><<<item_off[1], HIST_THREADS, smem, s>>>(d_nd.p, d_io.p, 1, chunk_rows, d_bins, ldb, d_labels, d_weights,
+                                                                 nrows, d_rows, nullptr, nullptr, d_loff.p, d_kind.p, C, d_hist, d_parent);
+    }
+    HAR_LAUNCH_CHECK();
+    HAR_CUDA(cudaStreamSynchronize(s));
+    return HAR_OK;
+}
+
+// =====================================================================================================
+HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, const double* d_y, const int32_t* arity,
+                           const int64_t* part_off_in, int32_t num_parts, const har_fit_params* p, const har_dist* dist,
+                           const uint8_t* d_weights_in, har_stream_t stream, har_forest_t** out) {
+    if (!out || !p) return fail(HAR_E_INVALID, "har_forest_fit: NULL params / out");
+    *out = nullptr;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int T = p->num_trees, C = p->num_classes, MB = p->max_bins;
+    if (p->max_depth < 0 || p->max_depth > 30)
+        return fail(HAR_E_INVALID, "DecisionTree currently only supports maxDepth <= 30, but was given maxDepth = %d.", p->max_depth);
+    if (MB < 2) return fail(HAR_E_INVALID, "maxBins must be >= 2, got %d", MB);
+    if (MB > HAR_MAX_BINS) return fail(HAR_E_UNSUPPORTED, "maxBins = %d exceeds this library's limit of %d", MB, HAR_MAX_BINS);
+    if (C < 2 || C > HAR_MAX_CLASSES) return fail(HAR_E_UNSUPPORTED, "numClasses = %d outside [2, %d]", C, HAR_MAX_CLASSES);
+    if (T < 1 || F < 1 || n < 0 || n > 0x7fffffff) return fail(HAR_E_INVALID, "har_forest_fit: bad num_trees / num_features / n");
+    if (p->min_instances_per_node < 1) return fail(HAR_E_INVALID, "minInstancesPerNode must be >= 1");
+    if (!(p->subsampling_rate > 0.0) || p->subsampling_rate > 1.0) return fail(HAR_E_INVALID, "subsamplingRate must be in (0, 1]");
+    if (p->features_per_node < 1 || p->features_per_node > F) return fail(HAR_E_INVALID, "features_per_node must be in [1, num_features]");
+    const int64_t n_global = dist ? dist->global_rows : n;
+    const int world = dist ? dist->world_size : 1;
+    if (n_global < 1) return fail(HAR_E_INVALID, "DecisionTree requires a non-empty training set");
+    int64_t po_default[2] = {0, n};
+    const int64_t* part_off = part_off_in;
+    if (!part_off) { part_off = po_default; num_parts = 1; }
+    const int part_offset = dist ? dist->partition_offset : 0;
+    const long long launches0 = launches_since_reset();
+
+    Meta m;
+    if (int rc = build_meta(m, F, C, n_global, MB, arity)) return rc;
+
+    // labels -> u8 (Classifier.extractLabeledPoints validation)
+    DevBuf<uint8_t> d_lab; DevBuf<unsigned long long> d_bad;
+    HAR_CUDA(d_lab.alloc(std::max<int64_t>(n, 1), s)); HAR_CUDA(d_bad.alloc(1, s));
+    HAR_CUDA(cudaMemsetAsync(d_bad.p, 0xff, sizeof(unsigned long long), s));
+    if (n) { k_labels_to_u8<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(d_y, n, C, d_lab.p, d_bad.p); HAR_LAUNCH_CHECK(); }
+    unsigned long long h_bad = 0;
+    HAR_CUDA(cudaMemcpyAsync(&h_bad, d_bad.p, sizeof h_bad, cudaMemcpyDeviceToHost, s));
+    HAR_CUDA(cudaStreamSynchronize(s));
+    if (h_bad != ~0ULL) {
+        double v = 0;
+        cudaMemcpy(&v, d_y + h_bad, sizeof(double), cudaMemcpyDeviceToHost);
+        return fail(HAR_E_INVALID, "Classifier given dataset with invalid label %g.  Labels must be integers in range [0, %d).", v, C);
+    }
+
+    std::unique_ptr<har_forest> fo(new har_forest());
+    fo->T = T; fo->C = C; fo->F = F; fo->max_bins = MB; fo->max_depth = p->max_depth;
+    fo->thresholds.assign((size_t)F * MB, 0.0);
+    fo->nsplits.assign(F, 0);
+    if (int rc = find_splits_impl(d_X, n, F, ld, m, MB, p->seed, part_off, num_parts, dist, fo->thresholds.data(),
+                                  fo->nsplits.data(), s)) return rc;
+    for (int f = 0; f < F; f++) if (m.arity[f] == 0) { m.num_splits[f] = fo->nsplits[f]; m.num_bins[f] = fo->nsplits[f] + 1; }
+    if (int rc = finish_meta(m)) return rc;
+    for (int f = 0; f < F; f++)
+        if (m.hist_bins[f] * C > HIST_TILE_WORDS) return fail(HAR_E_UNSUPPORTED, "feature %d needs more than %d counters", f, HIST_TILE_WORDS);
+
+    const int64_t ldb = (F + 15) & ~15;
+    DevBuf<uint8_t> d_bins;
+    HAR_CUDA(d_bins.alloc((size_t)std::max<int64_t>(n, 1) * ldb, s));
+    if (int rc = bin_features_impl(d_X, n, F, ld, arity, fo->thresholds.data(), fo->nsplits.data(), MB, d_bins.p, ldb, s)) return rc;
+
+    // bagging weights
+    const bool need_w = d_weights_in || !(T == 1 && p->subsampling_rate == 1.0);
+    DevBuf<uint8_t> d_wbuf;
+    const uint8_t* d_w = d_weights_in;
+    if (need_w && !d_weights_in) {
+        HAR_CUDA(d_wbuf.alloc((size_t)T * std::max<int64_t>(n, 1), s));
+        if (int rc = bag_weights_impl(n, T, p->subsampling_rate, p->seed, part_off, num_parts, part_offset, d_wbuf.p, s)) return rc;
+        d_w = d_wbuf.p;
+    }
+
+    // row permutations
+    DevBuf<int32_t> perm0, perm1, d_cnt, d_chunk;
+    const size_t perm_len = (size_t)T * std::max<int64_t>(n, 1);
+    HAR_CUDA(perm0.alloc(perm_len, s)); HAR_CUDA(perm1.alloc(perm_len, s));
+    std::vector<int32_t> root_cnt(T, (int32_t)n);
+    if (n) {
+        if (need_w) {
+            const int nchunks = (int)ceil_div(n, INIT_CHUNK);
+            HAR_CUDA(d_cnt.alloc(T, s)); HAR_CUDA(d_chunk.alloc((size_t)T * nchunks, s));
+            k_init_count<<<dim3(nchunks, T), 256, 0, s>>>(d_w, n, d_chunk.p, nchunks); HAR_LAUNCH_CHECK();
+            k_init_scan<<<(unsigned)ceil_div(T, 4), 128, 0, s>>>(d_chunk.p, nchunks, T, d_cnt.p); HAR_LAUNCH_CHECK();
+            k_init_scatter<<<dim3(nchunks, T), 256, 0, s>>>(d_w, n, d_chunk.p, nchunks, perm0.p); HAR_LAUNCH_CHECK();
+            HAR_CUDA(cudaMemcpyAsync(root_cnt.data(), d_cnt.p, sizeof(int32_t) * T, cudaMemcpyDeviceToHost, s));
+            HAR_CUDA(cudaStreamSynchronize(s));
+        } else {
+            k_iota<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(perm0.p, n); HAR_LAUNCH_CHECK();
+        }
+    }
+
+    // device-side metadata
+    DevBuf<uint8_t> d_kind; DevBuf<int32_t> d_nsplits, d_hbins, d_loff_all, d_flist_all;
+    HAR_CUDA(d_kind.alloc(F, s)); HAR_CUDA(d_nsplits.alloc(F, s)); HAR_CUDA(d_hbins.alloc(F, s));
+    HAR_CUDA(cudaMemcpyAsync(d_kind.p, m.kind.data(), F, cudaMemcpyHostToDevice, s));
+    HAR_CUDA(cudaMemcpyAsync(d_nsplits.p, m.num_splits.data(), sizeof(int32_t) * F, cudaMemcpyHostToDevice, s));
+    HAR_CUDA(cudaMemcpyAsync(d_hbins.p, m.hist_bins.data(), sizeof(int32_t) * F, cudaMemcpyHostToDevice, s));
+    FitMeta fm;
+    fm.kind = d_kind.p; fm.nsplits = d_nsplits.p; fm.hist_bins = d_hbins.p;
+    fm.C = C; fm.F = F; fm.max_depth = p->max_depth; fm.min_inst = p->min_instances_per_node; fm.impurity = p->impurity;
+    fm.min_gain = p->min_info_gain;
+
+    const bool subsample = p->features_per_node < F;
+    const int K = p->features_per_node;
+    int64_t total_bins_all = 0;
+    for (int f = 0; f < F; f++) total_bins_all += m.num_bins[f];
+    const int64_t full_len = m.loff[F];
+
+    // trees + node stack (RandomForest.run)
+    std::vector<std::vector<LNode>> trees(T);
+    std::vector<GroupItem> stack;
+    for (int t = 0; t < T; t++) {
+        LNode r; r.id = 1; r.stats.assign(C, 0.0); r.start = 0; r.count = root_cnt[t]; r.buf = 0;
+        trees[t].push_back(r);
+        stack.push_back({t, 0});
+    }
+    JavaRand rng(p->seed);
+
+    // batch buffers
+    const int64_t budget_words = 96LL << 20;                 // 384 MB of counters per device batch
+    DevBuf<uint32_t> d_hist;
+    DevBuf<NodeDesc> d_nodes;
+    DevBuf<NodeResult> d_res;
+    DevBuf<int32_t> d_item_off, d_chunk_left;
+    Pinned<NodeDesc> h_nodes; Pinned<NodeResult> h_res; Pinned<int32_t> h_item_off, h_sub;
+    size_t cap_nodes = 0, cap_hist = 0, cap_items = 0, cap_sub = 0;
+    if (!subsample) {
+        HAR_CUDA(d_loff_all.alloc(F + 1, s));
+        HAR_CUDA(cudaMemcpyAsync(d_loff_all.p, m.loff.data(), sizeof(int32_t) * (F + 1), cudaMemcpyHostToDevice, s));
+    }
+    const size_t hist_smem = (HIST_TILE_WORDS + 32) * sizeof(uint32_t);
+    HAR_CUDA(cudaFuncSetAttribute(k_node_hist<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem));
+    HAR_CUDA(cudaFuncSetAttribute(k_node_hist<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem));
+    const size_t bs_smem = ((size_t)BS_ROWS * (C + 1) + 64 * C) * 4 * (BS_THREADS / 32) + MAX_CAT * (BS_THREADS / 32) * 12 + 128 +
+                           sizeof(Cand) * (BS_THREADS / 32 + 1) + 64;
+    HAR_CUDA(cudaFuncSetAttribute(k_best_split, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
+
+    std::vector<GroupItem> group;
+    std::vector<NodeResult> group_res;
+    while (!stack.empty()) {
+        // ---- selectNodesToSplit ----
+        group.clear();
+        int64_t mem = 0;
+        while (!stack.empty()) {
+            GroupItem top = stack.back();
+            std::vector<int32_t> subset;
+            int64_t tb = total_bins_all;
+            if (subsample) {
+                subset.resize(K);
+                reservoir_features(F, K, rng.next_long(), subset.data());
+                tb = 0;
+                for (int j = 0; j < K; j++) tb += m.num_bins[subset[j]];
+            }
+            const int64_t cost = (int64_t)C * tb * 8;
+            if (mem + cost <= p->max_memory_bytes || mem == 0) {
+                stack.pop_back();
+                trees[top.tree][top.node].subset.swap(subset);
+                group.push_back(top);
+                mem += cost;
+            } else break;
+        }
+        fo->num_groups++;
+        const int64_t ng_total = (int64_t)group.size();
+        group_res.resize(ng_total);
+
+        // ---- findBestSplits, in device batches bounded by the counter budget ----
+        int64_t g0 = 0;
+        while (g0 < ng_total) {
+            int64_t g1 = g0, words = 0, rows_total = 0;
+            bool all_last_level = true;
+            while (g1 < ng_total) {
+                const LNode& nd = trees[group[g1].tree][group[g1].node];
+                int64_t len = full_len;
+                if (subsample) { len = 0; for (int f : nd.subset) len += (int64_t)m.hist_bins[f] * C; }
+                if (g1 > g0 && (words + len > budget_words || g1 - g0 >= (1 << 20))) break;
+                words += len; rows_total += nd.count;
+                if (level_of(nd.id) + 1 < p->max_depth) all_last_level = false;
+                g1++;
+            }
+            const int ng = (int)(g1 - g0);
+            fo->num_batches++;
+            int chunk_rows = (int)std::min<int64_t>(4096, std::max<int64_t>(256, rows_total / (kNumSMs * 8)));
+            chunk_rows = (chunk_rows + 255) & ~255;
+            // host-side descriptors
+            HAR_CUDA(h_nodes.reserve(ng)); HAR_CUDA(h_item_off.reserve(ng + 1)); HAR_CUDA(h_res.reserve(ng));
+            if (subsample) HAR_CUDA(h_sub.reserve((size_t)ng * (K + 1) * 2));
+            int64_t hb = 0, items = 0;
+            for (int g = 0; g < ng; g++) {
+                const LNode& nd = trees[group[g0 + g].tree][group[g0 + g].node];
+                NodeDesc& d = h_nodes.p[g];
+                d.start = nd.start; d.hist_base = hb; d.count = nd.count; d.tree = group[g0 + g].tree; d.buf = nd.buf;
+                d.level = level_of(nd.id); d.pad = 0;
+                if (subsample) {
+                    d.sub_off = g * (K + 1); d.nf = K;
+                    int32_t* fl = h_sub.p + (size_t)g * (K + 1);
+                    int32_t* lo = h_sub.p + (size_t)ng * (K + 1) + (size_t)g * (K + 1);
+                    int32_t off = 0;
+                    for (int j = 0; j < K; j++) { fl[j] = nd.subset[j]; lo[j] = off; off += m.hist_bins[nd.subset[j]] * C; }
+                    fl[K] = 0; lo[K] = off;
+                    d.hist_len = off;
+                } else { d.sub_off = 0; d.nf = F; d.hist_len = (int32_t)full_len; }
+                hb += d.hist_len;
+                h_item_off.p[g] = (int32_t)items;
+                items += ceil_div(nd.count, chunk_rows);
+            }
+            h_item_off.p[ng] = (int32_t)items;
+            if (items > 0x7fffffff) return fail(HAR_E_UNSUPPORTED, "too many work items in one batch");
+            // device buffers (grow-only)
+            if ((size_t)ng > cap_nodes) {
+                cap_nodes = (size_t)ng * 2;
+                HAR_CUDA(d_nodes.alloc(cap_nodes, s)); HAR_CUDA(d_res.alloc(cap_nodes, s)); HAR_CUDA(d_item_off.alloc(cap_nodes + 1, s));
+            }
+            const size_t need_hist = (size_t)hb + (size_t)ng * C;
+            if (need_hist > cap_hist) { cap_hist = need_hist + need_hist / 4; HAR_CUDA(d_hist.alloc(cap_hist, s)); }
+            if ((size_t)items + 1 > cap_items) { cap_items = (size_t)items * 2 + 1; HAR_CUDA(d_chunk_left.alloc(cap_items, s)); }
+            if (subsample && (size_t)ng * (K + 1) * 2 > cap_sub) {
+                cap_sub = (size_t)ng * (K + 1) * 4;
+                HAR_CUDA(d_flist_all.alloc(cap_sub, s));
+            }
+            const int32_t* flist_p = nullptr;
+            const int32_t* loff_p = d_loff_all.p;
+            if (subsample) {
+                HAR_CUDA(cudaMemcpyAsync(d_flist_all.p, h_sub.p, sizeof(int32_t) * (size_t)ng * (K + 1) * 2, cudaMemcpyHostToDevice, s));
+                flist_p = d_flist_all.p;
+                loff_p = d_flist_all.p + (size_t)ng * (K + 1);
+            }
+            HAR_CUDA(cudaMemcpyAsync(d_nodes.p, h_nodes.p, sizeof(NodeDesc) * ng, cudaMemcpyHostToDevice, s));
+            HAR_CUDA(cudaMemcpyAsync(d_item_off.p, h_item_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, s));
+            HAR_CUDA(cudaMemsetAsync(d_hist.p, 0, sizeof(uint32_t) * need_hist, s));
+            uint32_t* d_parent = d_hist.p + hb;
+            if (items > 0) {
+                prof_begin(s);
+                if (subsample)
+                    k_node_hist<true><<<(unsigned)items, HIST_THREADS, hist_smem, s>>>(d_nodes.p, d_item_off.p, ng, chunk_rows, d_bins.p, ldb,
+                        d_lab.p, d_w, n, perm0.p, perm1.p, flist_p, loff_p, d_kind.p, C, d_hist.p, d_parent);
+                else
+                    k_node_hist<false><<<(unsigned)items, HIST_THREADS, hist_smem, s>>>(d_nodes.p, d_item_off.p, ng, chunk_rows, d_bins.p, ldb,
+                        d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, d_hist.p, d_parent);
+                HAR_LAUNCH_CHECK();
+                prof_end(PROF_NODE_HIST, s, (double)rows_total);
+            }
+            // the only exchange on the path: reduceByKey(_.merge(_)) -> all-reduce of the batch's counters
+            if (int rc = dist_allreduce(dist, d_hist.p, (int64_t)need_hist, s)) return rc;
+            prof_begin(s);
+            k_best_split<<<ng, BS_THREADS, bs_smem, s>>>(d_nodes.p, ng, d_hist.p, d_parent, flist_p, loff_p, subsample ? 1 : 0, fm, d_res.p);
+            HAR_LAUNCH_CHECK();
+            prof_end(PROF_BEST_SPLIT, s, (double)ng);
+            if (!all_last_level && items > 0) {
+                prof_begin(s);
+                k_part_count<<<(unsigned)items, HIST_THREADS, 0, s>>>(d_nodes.p, d_item_off.p, ng, chunk_rows, d_res.p, d_bins.p, ldb, n,
+                                                                      perm0.p, perm1.p, d_chunk_left.p);
+                HAR_LAUNCH_CHECK();
+                prof_end(PROF_PART_COUNT, s, (double)rows_total);
+                k_part_scan<<<(unsigned)ceil_div(ng, 4), 128, 0, s>>>(d_item_off.p, ng, d_res.p, d_chunk_left.p);
+                HAR_LAUNCH_CHECK();
+                prof_begin(s);
+                k_part_scatter<<<(unsigned)items, HIST_THREADS, 0, s>>>(d_nodes.p, d_item_off.p, ng, chunk_rows, d_res.p, d_bins.p, ldb, n,
+                                                                        perm0.p, perm1.p, d_chunk_left.p);
+                HAR_LAUNCH_CHECK();
+                prof_end(PROF_PART_SCATTER, s, (double)rows_total);
+            }
+            HAR_CUDA(cudaMemcpyAsync(h_res.p, d_res.p, sizeof(NodeResult) * ng, cudaMemcpyDeviceToHost, s));
+            HAR_CUDA(cudaStreamSynchronize(s));
+            std::copy(h_res.p, h_res.p + ng, group_res.begin() + g0);
+            g0 = g1;
+        }
+
+        // ---- driver side of findBestSplits: children, leaf rules, stack pushes ----
+        std::vector<int> tkeys;
+        {
+            std::vector<char> seen(T, 0);
+            for (auto& gi : group) if (!seen[gi.tree]) { seen[gi.tree] = 1; tkeys.push_back(gi.tree); }
+        }
+        std::vector<int> torder = scala_hashmap_order(tkeys);
+        std::vector<std::vector<int>> by_tree(T);
+        for (int g = 0; g < (int)ng_total; g++) by_tree[group[g].tree].push_back(g);
+        for (int oi : torder) {
+            const int t = tkeys[oi];
+            for (int g : by_tree[t]) {
+                const NodeResult& r = group_res[g];
+                const int ni = group[g].node;
+                const int level = level_of(trees[t][ni].id);
+                const bool is_leaf = !(r.gain > 0.0) || level == p->max_depth;
+                {
+                    LNode& nd = trees[t][ni];
+                    nd.is_leaf = is_leaf; nd.valid = r.valid != 0; nd.gain = r.gain; nd.impurity = r.impurity;
+                    for (int c = 0; c < C; c++) nd.stats[c] = (double)r.parent[c];
+                    std::vector<int32_t>().swap(nd.subset);
+                }
+                if (is_leaf) continue;
+                const bool child_leaf = level + 1 == p->max_depth;
+                const bool ll = child_leaf || r.left_imp == 0.0, rl = child_leaf || r.right_imp == 0.0;
+                const bool parted = !(ll && rl);
+                LNode L, R;
+                L.id = trees[t][ni].id * 2; R.id = L.id + 1;
+                L.is_leaf = ll; R.is_leaf = rl; L.impurity = r.left_imp; R.impurity = r.right_imp;
+                L.stats.resize(C); R.stats.resize(C);
+                for (int c = 0; c < C; c++) { L.stats[c] = (double)r.left[c]; R.stats[c] = (double)r.right[c]; }
+                const LNode& pn = trees[t][ni];
+                L.start = pn.start; L.count = parted ? r.n_left : 0; L.buf = pn.buf ^ 1;
+                R.start = pn.start + L.count; R.count = parted ? pn.count - r.n_left : 0; R.buf = pn.buf ^ 1;
+                const int li = (int)trees[t].size();
+                trees[t].push_back(L); trees[t].push_back(R);
+                LNode& nd = trees[t][ni];
+                nd.left = li; nd.right = li + 1;
+                nd.feature = r.feature; nd.kind = r.kind; nd.split = r.split; nd.mask = r.left_mask; nd.arity = m.arity[r.feature];
+                nd.threshold = r.kind == KIND_CONT ? fo->thresholds[(size_t)r.feature * MB + r.split] : 0.0;
+                if (!ll) stack.push_back({t, li});
+                if (!rl) stack.push_back({t, li + 1});
+            }
+        }
+    }
+
+    // ---- toNode(prune = true) ----
+    fo->tree_off.assign(T + 1, 0);
+    for (int t = 0; t < T; t++) {
+        bool leaf = false;
+        fo->tree_off[t] = (int64_t)fo->feature.size();
+        emit_node(*fo, trees[t], 0, fo->tree_off[t], &leaf);
+    }
+    fo->tree_off[T] = (int64_t)fo->feature.size();
+    fo->num_launches = launches_since_reset() - launches0;
+    (void)world;
+    *out = fo.release();
+    return HAR_OK;
+}
+
+HAR_API int har_forest_shape(const har_forest_t* f, int32_t* num_trees, int32_t* num_classes, int32_t* num_features,
+                             int64_t* total_nodes) {
+    if (!f) return fail(HAR_E_INVALID, "har_forest_shape: NULL forest");
+    if (num_trees) *num_trees = f->T;
+    if (num_classes) *num_classes = f->C;
+    if (num_features) *num_features = f->F;
+    if (total_nodes) *total_nodes = (int64_t)f->feature.size();
+    return HAR_OK;
+}
+
+HAR_API int har_forest_export(const har_forest_t* f, int64_t* tree_off, int32_t* feature, int32_t* left, int32_t* right,
+                              int32_t* node_id, int32_t* arity, double* threshold, uint64_t* left_mask, double* prediction,
+                              double* impurity, double* gain, double* stats) {
+    if (!f) return fail(HAR_E_INVALID, "har_forest_export: NULL forest");
+    const size_t N = f->feature.size();
+    if (tree_off) std::copy(f->tree_off.begin(), f->tree_off.end(), tree_off);
+    if (feature) std::copy(f->feature.begin(), f->feature.end(), feature);
+    if (left) std::copy(f->left.begin(), f->left.end(), left);
+    if (right) std::copy(f->right.begin(), f->right.end(), right);
+    if (node_id && f->node_id.size() == N) std::copy(f->node_id.begin(), f->node_id.end(), node_id);
+    if (arity) std::copy(f->arity.begin(), f->arity.end(), arity);
+    if (threshold) std::copy(f->threshold.begin(), f->threshold.end(), threshold);
+    if (left_mask) std::copy(f->left_mask.begin(), f->left_mask.end(), left_mask);
+    if (prediction && f->prediction.size() == N) std::copy(f->prediction.begin(), f->prediction.end(), prediction);
+    if (impurity && f->impurity.size() == N) std::copy(f->impurity.begin(), f->impurity.end(), impurity);
+    if (gain && f->gain.size() == N) std::copy(f->gain.begin(), f->gain.end(), gain);
+    if (stats) std::copy(f->stats.begin(), f->stats.end(), stats);
+    return HAR_OK;
+}
+
+HAR_API int har_forest_fit_info(const har_forest_t* f, double* thresholds, int32_t* nsplits, int32_t max_bins,
+                                int64_t* num_groups, int64_t* num_batches, int64_t* num_kernel_launches) {
+    if (!f) return fail(HAR_E_INVALID, "har_forest_fit_info: NULL forest");
+    if ((thresholds || nsplits) && (max_bins != f->max_bins || f->nsplits.empty()))
+        return fail(HAR_E_INVALID, "har_forest_fit_info: forest was not fitted with max_bins = %d", max_bins);
+    if (thresholds) std::copy(f->thresholds.begin(), f->thresholds.end(), thresholds);
+    if (nsplits) std::copy(f->nsplits.begin(), f->nsplits.end(), nsplits);
+    if (num_groups) *num_groups = f->num_groups;
+    if (num_batches) *num_batches = f->num_batches;
+    if (num_kernel_launches) *num_kernel_launches = f->num_launches;
+    return HAR_OK;
+}

@@ -1,0 +1,313 @@
+"""Host-side plumbing between Arrow/numpy columns, torch device buffers and the C ABI.
+
+torch is used for device memory, streams and (in dist.py) torch.distributed only; every
+computation on the hot path is a kernel of libhar_b200.so.  Functions accept numpy arrays (copied
+host->device on the current stream) or CUDA tensors (used in place)."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _native as N
+
+WINDOW_FEATURE_NAMES = ([a + str(i) for a in "XYZ" for i in range(10)] +
+                        ["XAVG", "YAVG", "ZAVG", "XPEAK", "YPEAK", "ZPEAK", "XABSDEV", "YABSDEV", "ZABSDEV",
+                         "XSTDDEV", "YSTDDEV", "ZSTDDEV", "RESULTANT"])
+
+_TORCH = {np.dtype("float64"): torch.float64, np.dtype("int32"): torch.int32, np.dtype("int64"): torch.int64,
+          np.dtype("uint8"): torch.uint8}
+
+
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise N.HarError(-2, "har_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    N.lib()
+
+
+def stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def dev(a, dtype, pinned=False):
+    """numpy / tensor -> contiguous CUDA tensor of `dtype` on the current device."""
+    td = _TORCH[np.dtype(dtype)]
+    if isinstance(a, torch.Tensor):
+        if a.is_cuda and a.dtype == td and a.is_contiguous():
+            return a
+        return a.to(device="cuda", dtype=td).contiguous()
+    a = np.ascontiguousarray(a, dtype=dtype)
+    t = torch.from_numpy(a)
+    if pinned:
+        t = t.pin_memory()
+    return t.cuda(non_blocking=pinned)
+
+
+def matrix(X):
+    """-> (CUDA f64 tensor, n, F, ld) for a row-major matrix; keeps a strided CUDA view in place."""
+    if isinstance(X, torch.Tensor) and X.is_cuda and X.dtype == torch.float64 and X.dim() == 2 and X.stride(1) == 1:
+        return X, X.shape[0], X.shape[1], (X.stride(0) if X.shape[0] > 1 else max(X.stride(0), X.shape[1]))
+    t = dev(X, np.float64)
+    if t.dim() != 2:
+        raise ValueError("expected a 2-d feature matrix")
+    return t, t.shape[0], t.shape[1], t.shape[1]
+
+
+def ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def hptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def parts(n, part_off):
+    po = np.ascontiguousarray([0, n] if part_off is None else part_off, dtype=np.int64)
+    if po[0] != 0 or po[-1] != n or np.any(np.diff(po) < 0):
+        raise ValueError("part_off must be non-decreasing from 0 to n")
+    return po
+
+
+def launch_count(reset=False):
+    return int(N.lib().har_debug_launch_count(1 if reset else 0))
+
+
+PROFILE_IDS = ("node_hist", "best_split", "part_count", "part_scatter", "window_features", "seg_tiles", "predict",
+               "bin_features", "find_splits", "bag_weights")
+
+
+def profile(enable=None, reset=False):
+    """CUDA-event timing of selected kernels, measured inside the library on the launching stream.
+    Returns {kernel: (total_ms, launches, units)} accumulated since the last reset."""
+    L = N.lib()
+    if enable is not None:
+        L.har_debug_profile_enable(1 if enable else 0)
+    out = {}
+    for i, name in enumerate(PROFILE_IDS):
+        ms, ln, un = C.c_double(), C.c_longlong(), C.c_double()
+        L.har_debug_profile_read(i, C.byref(ms), C.byref(ln), C.byref(un))
+        out[name] = (ms.value, ln.value, un.value)
+    if reset:
+        L.har_debug_profile_reset()
+    return out
+
+
+# ---- window transform ------------------------------------------------------------------------------
+def window_segments(user, activity, ts=None, window_len=200, gap_ns=0):
+    require_cuda()
+    u, a = dev(user, np.int32), dev(activity, np.int32)
+    t = None if ts is None else dev(ts, np.int64)
+    n = u.numel()
+    cap = max(n // window_len, 1)
+    ws = torch.empty(cap, dtype=torch.int64, device="cuda")
+    wu = torch.empty(cap, dtype=torch.int32, device="cuda")
+    wa = torch.empty(cap, dtype=torch.int32, device="cuda")
+    nw = C.c_int64(0)
+    N.check(N.lib().har_window_segments(ptr(u), ptr(a), ptr(t), n, window_len, gap_ns, ptr(ws), ptr(wu), ptr(wa),
+                                        C.byref(nw), stream()))
+    k = nw.value
+    return ws[:k], wu[:k], wa[:k]
+
+
+def window_features(x, y, z, ts, win_start, window_len=200, out=None):
+    require_cuda()
+    xd, yd, zd, td = dev(x, np.float64), dev(y, np.float64), dev(z, np.float64), dev(ts, np.int64)
+    ws = dev(win_start, np.int64)
+    nw = ws.numel()
+    if out is None:
+        out = torch.empty((nw, N.NUM_WINDOW_FEATURES), dtype=torch.float64, device="cuda")
+    N.check(N.lib().har_window_features(ptr(xd), ptr(yd), ptr(zd), ptr(td), xd.numel(), ptr(ws), nw, window_len,
+                                        ptr(out), out.stride(0) if nw > 1 else N.NUM_WINDOW_FEATURES, stream()))
+    return out
+
+
+# ---- tree stages -----------------------------------------------------------------------------------
+def resolve_features_per_node(strategy, F, num_trees):
+    """DecisionTreeMetadata.buildMetadata's featureSubsetStrategy (classification), SURVEY A.5."""
+    s = str(strategy).lower()
+    if s == "auto":
+        s = "all" if num_trees == 1 else "sqrt"
+    if s == "all":
+        return F
+    if s == "sqrt":
+        return int(np.ceil(np.sqrt(F)))
+    if s == "log2":
+        return max(1, int(np.ceil(np.log(F) / np.log(2))))
+    if s == "onethird":
+        return int(np.ceil(F / 3.0))
+    try:
+        k = int(s)
+    except ValueError:
+        k = None
+    if k is not None:
+        if k > 0:
+            return min(k, F)
+    else:
+        try:
+            fr = float(s)
+        except ValueError:
+            fr = -1.0
+        if 0.0 < fr <= 1.0:
+            return int(np.ceil(fr * F))
+    raise ValueError("Supported values: auto, all, onethird, sqrt, log2, (0.0-1.0], [1-n]. Got %r" % (strategy,))
+
+
+def find_splits(X, arity=None, max_bins=32, seed=0, part_off=None, dist=None):
+    require_cuda()
+    Xd, n, F, ld = matrix(X)
+    ar = None if arity is None else np.ascontiguousarray(arity, np.int32)
+    po = parts(n, part_off)
+    thr = np.zeros((F, max_bins)); ns = np.zeros(F, np.int32)
+    N.check(N.lib().har_find_splits(ptr(Xd), n, F, ld, hptr(ar), max_bins, seed, hptr(po), len(po) - 1,
+                                    None if dist is None else C.byref(dist.struct), hptr(thr), hptr(ns), stream()))
+    return thr, ns
+
+
+def bin_features(X, thresholds, nsplits, arity=None):
+    require_cuda()
+    Xd, n, F, ld = matrix(X)
+    ar = None if arity is None else np.ascontiguousarray(arity, np.int32)
+    thr = np.ascontiguousarray(thresholds, np.float64)
+    ldb = (F + 15) & ~15
+    bins = torch.zeros((max(n, 1), ldb), dtype=torch.uint8, device="cuda")
+    N.check(N.lib().har_bin_features(ptr(Xd), n, F, ld, hptr(ar), hptr(thr), hptr(np.ascontiguousarray(nsplits, np.int32)),
+                                     thr.shape[1], ptr(bins), ldb, stream()))
+    return bins[:n]
+
+
+def bag_weights(n, num_trees, rate=1.0, seed=0, part_off=None, partition_offset=0):
+    require_cuda()
+    po = parts(n, part_off)
+    w = torch.empty((num_trees, n), dtype=torch.uint8, device="cuda")
+    N.check(N.lib().har_bag_weights(n, num_trees, float(rate), seed, hptr(po), len(po) - 1, partition_offset, ptr(w), stream()))
+    return w
+
+
+def node_histogram(bins, labels, hist_off, num_classes, weights=None, rows=None):
+    require_cuda()
+    b = dev(bins, np.uint8)
+    lab = dev(labels, np.uint8)
+    w = None if weights is None else dev(weights, np.uint8)
+    r = None if rows is None else dev(rows, np.int32)
+    ho = np.ascontiguousarray(hist_off, np.int64)
+    F = len(ho) - 1
+    hist = torch.zeros(int(ho[-1]), dtype=torch.int32, device="cuda")
+    parent = torch.zeros(num_classes, dtype=torch.int32, device="cuda")
+    nrows = b.shape[0] if r is None else r.numel()
+    N.check(N.lib().har_node_histogram(ptr(b), b.stride(0), ptr(lab), ptr(w), ptr(r), nrows, F, num_classes, hptr(ho),
+                                       ptr(hist), ptr(parent), stream()))
+    return hist, parent
+
+
+class Forest:
+    """Owns a har_forest_t*; flat arrays are exported once to numpy (see har_forest_export)."""
+    FIELDS = ("tree_off", "feature", "left", "right", "node_id", "arity", "threshold", "left_mask",
+              "prediction", "impurity", "gain", "stats")
+
+    def __init__(self, handle):
+        self._h = C.c_void_p(handle)
+        T, Cn, F, tot = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int64()
+        N.check(N.lib().har_forest_shape(self._h, C.byref(T), C.byref(Cn), C.byref(F), C.byref(tot)))
+        self.T, self.C, self.F, self.total_nodes = T.value, Cn.value, F.value, tot.value
+        n = self.total_nodes
+        self.tree_off = np.zeros(self.T + 1, np.int64)
+        self.feature = np.zeros(n, np.int32); self.left = np.zeros(n, np.int32); self.right = np.zeros(n, np.int32)
+        self.node_id = np.zeros(n, np.int32); self.arity = np.zeros(n, np.int32)
+        self.threshold = np.zeros(n, np.float64); self.left_mask = np.zeros(n, np.uint64)
+        self.prediction = np.zeros(n, np.float64); self.impurity = np.zeros(n, np.float64)
+        self.gain = np.zeros(n, np.float64); self.stats = np.zeros((n, self.C), np.float64)
+        N.check(N.lib().har_forest_export(self._h, *[hptr(getattr(self, k)) for k in self.FIELDS]))
+        self.thresholds = self.nsplits = None
+        self.num_groups = self.num_batches = self.num_launches = 0
+
+    @classmethod
+    def from_arrays(cls, T, Cn, F, tree_off, feature, left, right, arity, threshold, left_mask, stats):
+        N.lib()
+        h = C.c_void_p()
+        arrs = [np.ascontiguousarray(tree_off, np.int64), np.ascontiguousarray(feature, np.int32),
+                np.ascontiguousarray(left, np.int32), np.ascontiguousarray(right, np.int32),
+                np.ascontiguousarray(arity, np.int32), np.ascontiguousarray(threshold, np.float64),
+                np.ascontiguousarray(left_mask, np.uint64), np.ascontiguousarray(stats, np.float64)]
+        N.check(N.lib().har_forest_import(T, Cn, F, *[hptr(a) for a in arrs], C.byref(h)))
+        return cls(h.value)
+
+    def _load_fit_info(self, max_bins):
+        self.thresholds = np.zeros((self.F, max_bins)); self.nsplits = np.zeros(self.F, np.int32)
+        g, b, l = C.c_int64(), C.c_int64(), C.c_int64()
+        N.check(N.lib().har_forest_fit_info(self._h, hptr(self.thresholds), hptr(self.nsplits), max_bins,
+                                            C.byref(g), C.byref(b), C.byref(l)))
+        self.num_groups, self.num_batches, self.num_launches = g.value, b.value, l.value
+
+    def tree_num_nodes(self, t):
+        return int(self.tree_off[t + 1] - self.tree_off[t])
+
+    def tree_depth(self, t):
+        base = int(self.tree_off[t])
+        depth = {0: 0}
+        best = 0
+        for k in range(self.tree_num_nodes(t)):          # pre-order: parents precede children
+            if self.feature[base + k] >= 0:
+                d = depth[k] + 1
+                depth[int(self.left[base + k])] = d
+                depth[int(self.right[base + k])] = d
+                best = max(best, d)
+        return best
+
+    def predict(self, X, is_forest=None, want=("raw", "prob", "pred")):
+        require_cuda()
+        Xd, n, F, ld = matrix(X)
+        if F != self.F:
+            raise ValueError("feature matrix has %d columns, the model was trained on %d" % (F, self.F))
+        if is_forest is None:
+            is_forest = self.T > 1
+        raw = torch.empty((n, self.C), dtype=torch.float64, device="cuda") if "raw" in want else None
+        prob = torch.empty((n, self.C), dtype=torch.float64, device="cuda") if "prob" in want else None
+        pred = torch.empty(n, dtype=torch.float64, device="cuda") if "pred" in want else None
+        N.check(N.lib().har_forest_predict(self._h, ptr(Xd), n, ld, 1 if is_forest else 0, ptr(raw), ptr(prob), ptr(pred),
+                                           stream()))
+        return raw, prob, pred
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            N.lib().har_forest_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def fit_forest(X, y, arity=None, num_classes=None, num_trees=1, max_depth=5, max_bins=32,
+               min_instances_per_node=1, min_info_gain=0.0, impurity="gini", feature_subset="auto",
+               subsampling_rate=1.0, seed=0, max_memory_mb=256, part_off=None, weights=None, dist=None):
+    """RandomForest.run on the GPU (har_forest_fit).  X: [n, F] f64 (numpy or CUDA tensor), y: [n] f64."""
+    require_cuda()
+    Xd, n, F, ld = matrix(X)
+    yd = dev(y, np.float64)
+    if yd.numel() != n:
+        raise ValueError("labels and features disagree on the number of rows")
+    if num_classes is None:
+        num_classes = int(yd.max().item()) + 1 if n else 2
+    if impurity not in ("gini", "entropy"):
+        raise ValueError("impurity must be 'gini' or 'entropy'")
+    ar = None if arity is None else np.ascontiguousarray(arity, np.int32)
+    po = parts(n, part_off)
+    p = N.FitParams(num_trees, max_depth, max_bins, num_classes, min_instances_per_node,
+                    0 if impurity == "gini" else 1, resolve_features_per_node(feature_subset, F, num_trees), 0,
+                    float(min_info_gain), float(subsampling_rate), int(seed), int(max_memory_mb) * 1024 * 1024)
+    w = None if weights is None else dev(weights, np.uint8)
+    h = C.c_void_p()
+    N.check(N.lib().har_forest_fit(ptr(Xd), n, F, ld, ptr(yd), hptr(ar), hptr(po), len(po) - 1, C.byref(p),
+                                   None if dist is None else C.byref(dist.struct), ptr(w), stream(), C.byref(h)))
+    fo = Forest(h.value)
+    fo._load_fit_info(max_bins)
+    return fo
+
+
+def csr_to_dense(indptr, indices, values, n, F):
+    require_cuda()
+    ip, ix, vv = dev(indptr, np.int64), dev(indices, np.int32), dev(values, np.float64)
+    out = torch.empty((n, F), dtype=torch.float64, device="cuda")
+    N.check(N.lib().har_csr_to_dense(ptr(ip), ptr(ix), ptr(vv), n, F, ptr(out), F, stream()))
+    return out

@@ -1,0 +1,64 @@
+"""Multi-GPU plumbing: one process per GPU, rows sharded by Spark partition, the only exchange is
+the all-reduce of node-group histograms done by torch.distributed (NCCL over
+NVLink) through the har_allreduce_i32_fn callback of include/har_b200.h."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _native as N
+
+
+def shard_partitions(total_partitions, rank, world_size):
+    """Contiguous, balanced partition range [p0, p1) owned by `rank`."""
+    base, rem = divmod(total_partitions, world_size)
+    p0 = rank * base + min(rank, rem)
+    return p0, p0 + base + (1 if rank < rem else 0)
+
+
+def shard_rows(global_part_off, rank, world_size):
+    """-> (row0, row1, local part_off, partition_offset) for this rank."""
+    gpo = np.ascontiguousarray(global_part_off, dtype=np.int64)
+    p0, p1 = shard_partitions(len(gpo) - 1, rank, world_size)
+    r0, r1 = int(gpo[p0]), int(gpo[p1])
+    return r0, r1, gpo[p0:p1 + 1] - r0, p0
+
+
+class _DevPtr:
+    def __init__(self, ptr, count):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": "<i4", "data": (ptr, False), "version": 2}
+
+
+def wrap_i32(ptr, count, device=None):
+    """int32 view of `count` elements at a raw pointer: CUDA (device given) or host memory."""
+    if device is not None:
+        return torch.as_tensor(_DevPtr(ptr, count), device=device)
+    buf = (C.c_int32 * count).from_address(ptr)
+    return torch.frombuffer(buf, dtype=torch.int32)
+
+
+class Dist:
+    """Builds the har_dist struct; keeps the ctypes callback alive."""
+
+    def __init__(self, global_rows, partition_offset, total_partitions, group=None, host_buffers=False):
+        import torch.distributed as td
+        self._td, self._group = td, group
+        self.rank, self.world = td.get_rank(group), td.get_world_size(group)
+        self._device = None if host_buffers else torch.device("cuda", torch.cuda.current_device())
+        self.calls = 0
+        self.bytes = 0
+
+        def _cb(ctx, ptr, count, stream):
+            try:
+                t = wrap_i32(ptr, count, self._device)
+                td.all_reduce(t, op=td.ReduceOp.SUM, group=self._group)
+                self.calls += 1
+                self.bytes += 4 * count
+                return 0
+            except Exception as e:      # never let an exception cross the C boundary
+                print("har_b200 all-reduce callback failed:", repr(e))
+                return 1
+
+        self._cb = N.ALLREDUCE_FN(_cb)
+        self.struct = N.Dist(self.rank, self.world, int(global_rows), int(partition_offset), int(total_partitions),
+                             self._cb, None)

@@ -974,12 +974,12 @@ ORC_API void orc_window_features(const double* x, const double* y, const double*
             double mean = sum / (double)L;
             double sq = 0, ab = 0;
             int cnt[10] = {0};
-            double wdt = (hi - lo) / 10.0;
+            double scale = hi > lo ? 10.0 / (hi - lo) : 0.0;
             for (int i = 0; i < L; i++) {
                 double d = v[i] - mean;
                 sq += d * d; ab += fabs(d);
                 int b = 0;
-                if (hi > lo) { double q = floor((v[i] - lo) / wdt); b = q >= 9.0 ? 9 : (int)q; if (b < 0) b = 0; }
+                { double q = floor((v[i] - lo) * scale); b = q >= 9.0 ? 9 : (int)q; }
                 cnt[b]++;
             }
             for (int b = 0; b < 10; b++) o[a * 10 + b] = (double)cnt[b] / (double)L;
