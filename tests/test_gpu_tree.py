@@ -20,7 +20,8 @@ def _bits(a):
                                                  (12000, 50, 100), (5, None, 32)])
 def test_find_splits_and_binning_bit_exact(n, quantize, max_bins):
     from har_b200 import core
-    X, y, arity = synth_tree_data(n, F=9, seed=n, n_cat_unordered=1, n_cat_ordered=1, quantize=quantize)
+    X, y, arity = synth_tree_data(n, F=9, seed=n, n_cat_unordered=1, n_cat_ordered=1 if max_bins >= 9 and n >= 9 else 0,
+                                  quantize=quantize)
     X[:, 5] = 1.5                      # constant feature: no splits
     X[::7, 6] = 0.0
     po = [0, n // 3, n]
