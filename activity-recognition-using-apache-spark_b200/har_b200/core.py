@@ -18,6 +18,17 @@ _TORCH = {np.dtype("float64"): torch.float64, np.dtype("int32"): torch.int32, np
           np.dtype("uint8"): torch.uint8}
 
 
+COUNTERS = {"h2d_bytes": 0, "d2h_bytes": 0}      # host<->device traffic moved by this layer (bench.py's e2e)
+
+
+def to_host(t):
+    """CUDA tensor -> numpy (counted device->host copy)."""
+    if t is None:
+        return None
+    COUNTERS["d2h_bytes"] += t.numel() * t.element_size()
+    return t.cpu().numpy()
+
+
 def require_cuda():
     if not torch.cuda.is_available():
         raise N.HarError(-2, "har_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
@@ -37,9 +48,9 @@ def dev(a, dtype, pinned=False):
         return a.to(device="cuda", dtype=td).contiguous()
     a = np.ascontiguousarray(a, dtype=dtype)
     t = torch.from_numpy(a)
-    if pinned:
-        t = t.pin_memory()
-    return t.cuda(non_blocking=pinned)
+    COUNTERS["h2d_bytes"] += a.nbytes
+    # non_blocking is honoured only for page-locked memory (callers that care keep their columns pinned)
+    return t.cuda(non_blocking=True)
 
 
 def matrix(X):

@@ -62,3 +62,16 @@ class Dist:
         self._cb = N.ALLREDUCE_FN(_cb)
         self.struct = N.Dist(self.rank, self.world, int(global_rows), int(partition_offset), int(total_partitions),
                              self._cb, None)
+
+
+def exchange_shard_layout(local_rows, local_partitions, group=None):
+    """-> (global_rows, this rank's first global partition index, total partitions), by all-gather."""
+    import torch.distributed as td
+    dev = torch.device("cuda", torch.cuda.current_device()) if td.get_backend(group) == "nccl" else torch.device("cpu")
+    mine = torch.tensor([int(local_rows), int(local_partitions)], dtype=torch.int64, device=dev)
+    allv = [torch.zeros_like(mine) for _ in range(td.get_world_size(group))]
+    td.all_gather(allv, mine, group=group)
+    rows = [int(v[0]) for v in allv]
+    parts = [int(v[1]) for v in allv]
+    r = td.get_rank(group)
+    return sum(rows), sum(parts[:r]), sum(parts)

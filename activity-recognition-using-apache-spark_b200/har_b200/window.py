@@ -65,14 +65,14 @@ class WisdmWindowFeaturizer(Transformer):
             c[dataset._resolve(self.getUserCol())], c[dataset._resolve(self.getActivityCol())],
             c[dataset._resolve(self.getTimestampCol())], c[dataset._resolve(self.getXCol())],
             c[dataset._resolve(self.getYCol())], c[dataset._resolve(self.getZCol())])
-        f = feats.cpu().numpy()
+        f = core.to_host(feats)
         nw = f.shape[0]
         cols, types = {}, {}
         cols["UID"], types["UID"] = np.arange(1, nw + 1, dtype=np.int32), "int"
-        cols["USER"], types["USER"] = wu.cpu().numpy(), "int"
+        cols["USER"], types["USER"] = core.to_host(wu), "int"
         for j, name in enumerate(core.WINDOW_FEATURE_NAMES):
             cols[name], types[name] = np.ascontiguousarray(f[:, j]), "double"
-        cols["ACTIVITY"], types["ACTIVITY"] = wa.cpu().numpy(), "int"
+        cols["ACTIVITY"], types["ACTIVITY"] = core.to_host(wa), "int"
         meta = {}
         if self.isDefined(self.outputCol):
             fv = np.where(np.isnan(f), self.getUnknownPeakValue(), f)

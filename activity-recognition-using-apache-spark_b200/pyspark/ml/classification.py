@@ -99,12 +99,23 @@ class _TreeEstimatorBase(Estimator, _TreeClassifierParams):
         if imp not in ("gini", "entropy"):
             raise ValueError("impurity given invalid value %r" % imp)
         X = _device_features(col)
+        part_off, dist = dataset._partitions, None
+        try:
+            import torch.distributed as td
+            multi = td.is_available() and td.is_initialized() and td.get_world_size() > 1
+        except Exception:
+            multi = False
+        if multi:
+            # one process per GPU, each holding its row shard of the frame: a collective fit
+            from har_b200.dist import Dist, exchange_shard_layout
+            global_rows, p_off, p_total = exchange_shard_layout(len(y), len(part_off) - 1)
+            dist = Dist(global_rows, p_off, p_total)
         forest = core.fit_forest(
             X, y, arity=arity, num_classes=C, num_trees=num_trees, max_depth=self.getMaxDepth(),
             max_bins=self.getMaxBins(), min_instances_per_node=self.getMinInstancesPerNode(),
             min_info_gain=self.getMinInfoGain(), impurity=imp, feature_subset=feature_subset,
             subsampling_rate=subsampling_rate, seed=self.getSeed(), max_memory_mb=self.getMaxMemoryInMB(),
-            part_off=dataset._partitions)
+            part_off=part_off, dist=dist)
         return forest, col.size, C
 
 
@@ -137,8 +148,9 @@ class _TreeModelBase(Model, _TreeClassifierParams):
         fname = dataset._resolve(self.getFeaturesCol())
         col = dataset._cols[fname]
         X = _device_features(col)
+        from har_b200 import core
         raw, prob, pred = forest.predict(X, is_forest=is_forest)
-        raw, prob, pred = raw.cpu().numpy(), prob.cpu().numpy(), pred.cpu().numpy()
+        raw, prob, pred = core.to_host(raw), core.to_host(prob), core.to_host(pred)
         if self.isDefined(self.thresholds) and self.getOrDefault(self.thresholds) is not None:
             th = np.asarray(self.getOrDefault(self.thresholds), dtype=np.float64)
             if len(th) != forest.C:

@@ -78,10 +78,11 @@ int har_window_features(const double* d_x, const double* d_y, const double* d_z,
 /* Synthetic tri-axial stream of SURVEY §8(d) (bench / test input; counter-based so the CPU oracle
  * produces the same bits).  Bout table: host arrays, bout b covers global samples
  * [bout_start[b], bout_start[b+1]) of user bout_user[b] doing bout_activity[b]; `first_sample`
- * is the global index of local sample 0.  tables: sine[1024], mu/amp/sigma[6*3], freq[6]. */
+ * is the global index of local sample 0; bout_gain / bout_tilt scale the carrier and tilt the mean per
+ * bout so that classes overlap.  tables: sine[1024], mu/amp/sigma[6*3], freq[6]. */
 int har_synth_stream(int64_t n, int64_t first_sample, uint64_t seed,
                      const int64_t* bout_start, const int32_t* bout_user, const int32_t* bout_activity,
-                     const int64_t* bout_ts0, int64_t num_bouts,
+                     const int64_t* bout_ts0, const double* bout_gain, const double* bout_tilt, int64_t num_bouts,
                      const double* sine1024, const double* mu, const double* amp, const double* sigma,
                      const int32_t* freq,
                      int32_t* d_user, int32_t* d_activity, int64_t* d_ts,

@@ -1021,6 +1021,9 @@ ORC_API void orc_synth_stream(int64_t n, int64_t first_sample, int64_t per_user,
             int64_t len = 600 + (int64_t)(h % 5400);
             int a = (int)((h >> 32) % 6);
             if (a == prev_act) a = (a + 1) % 6;
+            const double gain = 0.35 + 1.3 * ((double)((h >> 8) & 0xffff) / 65535.0);
+            const double tilt = (double)((h >> 24) & 0xffff) / 65535.0 - 0.5;
+            static const double tiltv[3] = {3.0, -4.0, 3.5};
             int64_t b1 = b0 + len; if (b1 > uend) b1 = uend;
             if (g < b1) {
                 int64_t stop = b1 - first_sample; if (stop > n) stop = n;
@@ -1034,8 +1037,9 @@ ORC_API void orc_synth_stream(int64_t n, int64_t first_sample, int64_t per_user,
                         int64_t nz = (int64_t)(r & 0xffff) + (int64_t)((r >> 16) & 0xffff) +
                                      (int64_t)((r >> 32) & 0xffff) + (int64_t)((r >> 48) & 0xffff) - 2 * 65535;
                         double noise = (double)nz * (sigma[a * 3 + ax] * (1.0 / 37837.0));
-                        double car = amp[a * 3 + ax] * sine1024[(uint64_t)(k * freq[a] + ax * 85) & 1023];
-                        outp[ax][i] = (mu[a * 3 + ax] + car) + noise;
+                        /* per-bout gain / tilt (from the bout hash) make the six classes overlap */
+                        double car = (amp[a * 3 + ax] * gain) * sine1024[(uint64_t)(k * freq[a] + ax * 85) & 1023];
+                        outp[ax][i] = ((mu[a * 3 + ax] + tilt * tiltv[ax]) + car) + noise;
                     }
                 }
                 break;

@@ -232,13 +232,13 @@ def window_features(x, y, z, ts, win_start, L=200):
 
 
 # ---- synthetic stream -------------------------------------------------------------
-SYNTH_MU = np.array([[0.6, 9.6, 0.4], [0.3, 8.9, 1.1], [-0.4, 9.1, 1.6], [0.5, 9.0, -0.9],
-                     [2.1, 6.2, 7.1], [0.2, 9.8, 0.3]], dtype=np.float64)
-SYNTH_AMP = np.array([[2.4, 3.9, 2.2], [5.8, 7.6, 4.4], [3.1, 4.3, 3.0], [2.9, 4.6, 2.7],
-                      [0.05, 0.05, 0.05], [0.1, 0.12, 0.1]], dtype=np.float64)
-SYNTH_SIGMA = np.array([[1.2, 1.6, 1.1], [2.2, 2.6, 1.9], [1.5, 1.9, 1.4], [1.6, 1.8, 1.5],
-                        [0.08, 0.08, 0.08], [0.15, 0.18, 0.15]], dtype=np.float64)
-SYNTH_FREQ = np.array([97, 143, 83, 89, 7, 11], dtype=np.int32)       # table steps per sample
+SYNTH_MU = np.array([[0.6, 9.3, 0.4], [0.5, 9.1, 0.7], [0.3, 9.2, 0.9], [0.5, 9.2, 0.5],
+                     [1.1, 8.2, 2.1], [0.4, 9.4, 0.6]], dtype=np.float64)
+SYNTH_AMP = np.array([[3.0, 4.2, 2.6], [4.4, 5.6, 3.4], [3.1, 4.3, 3.0], [2.9, 4.4, 2.7],
+                      [0.6, 0.7, 0.5], [0.8, 0.9, 0.7]], dtype=np.float64)
+SYNTH_SIGMA = np.array([[2.2, 2.6, 2.1], [2.6, 3.0, 2.3], [2.3, 2.7, 2.2], [2.4, 2.6, 2.2],
+                        [1.1, 1.2, 1.0], [1.2, 1.3, 1.1]], dtype=np.float64)
+SYNTH_FREQ = np.array([97, 113, 89, 93, 41, 47], dtype=np.int32)       # table steps per sample
 SYNTH_SINE = np.sin(2.0 * np.pi * np.arange(1024) / 1024.0)
 
 
