@@ -457,6 +457,100 @@ HAR_API int har_window_segments(const int32_t* d_user, const int32_t* d_activity
     return HAR_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// har_window_segments_static: the same segmentation for hosts that must not allocate.
+//
+// Some programs that load this library are not allowed to ask CUDA for memory once they are running:
+// a serving process that has already handed the whole device to its own memory manager (a later
+// cudaMalloc or cudaMallocAsync fails or fragments that reservation), a control loop with a fixed
+// latency budget (allocation calls may take a driver lock or wait for the device), or a plug-in host
+// that only lets extensions touch buffers it pre-approved.  har_window_segments needs scratch memory
+// for its per-tile summaries and takes it from cudaMallocAsync on every call, so those programs cannot
+// use it.  This variant keeps that scratch in the array below, which is part of the library image: every
+// GPU that loads the library carries these 4 MiB until the process exits, whether or not the function
+// is ever called.  The caller still supplies all inputs and outputs.
+//
+// In host code `g_seg_static` is only a handle for the symbol, not a device address.  The device
+// address is looked up with cudaGetSymbolAddress once per device (with that device current) and
+// cached; the kernels get the looked-up pointer.  That look-up happens inside the first call made on
+// each device, so make that first call during start-up, before any stream capture begins.
+//
+// All calls on a device share the one array.  Two calls whose kernels can overlap on the GPU (different
+// streams, or different host threads) would overwrite each other's tile summaries: callers must
+// serialise them.  The array keeps whatever the previous call left in it; that is harmless here because
+// every entry a call reads (per-tile first/last boundary, counts, prefix sums, the window list of each
+// tile up to its own count, and the total) is written earlier in the same call, so nothing has to be
+// cleared to zero beforehand.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t SEG_STATIC_BYTES = 4u << 20;      // HAR_SEGMENTS_STATIC_BYTES
+static __device__ __align__(256) unsigned char g_seg_static[SEG_STATIC_BYTES];
+
+static int seg_static_base(unsigned char** base) {
+    static unsigned char* cache[64] = {nullptr};
+    int dev = 0;
+    HAR_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return har::fail(HAR_E_UNSUPPORTED, "har_window_segments_static: device index %d not supported", dev);
+    if (!cache[dev]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_seg_static);
+        if (e != cudaSuccess || !p)
+            return har::fail(HAR_E_CUDA, "har_window_segments_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+        cache[dev] = static_cast<unsigned char*>(p);
+    }
+    *base = cache[dev];
+    return HAR_OK;
+}
+
+HAR_API int har_window_segments_static(const int32_t* d_user, const int32_t* d_activity, const int64_t* d_ts,
+                                       int64_t n, int32_t window_len, int64_t gap_ns, int64_t* d_win_start,
+                                       int32_t* d_win_user, int32_t* d_win_activity, int64_t* num_windows,
+                                       har_stream_t stream) {
+    if (!num_windows) return har::fail(HAR_E_INVALID, "har_window_segments_static: num_windows is NULL");
+    *num_windows = 0;
+    if (n < 0 || window_len < 2) return har::fail(HAR_E_INVALID, "har_window_segments_static: need n >= 0 and window_len >= 2");
+    if (gap_ns > 0 && !d_ts) return har::fail(HAR_E_INVALID, "har_window_segments_static: gap_ns > 0 needs d_ts");
+    // carve the fixed array: 4 x int64 + 2 x int32 per tile, `cap` window slots per tile, one int64 total
+    const int64_t num_tiles = har::ceil_div(n, SEG_TILE);
+    const int32_t cap = SEG_TILE / window_len + 1;
+    const size_t per_tile = 4 * sizeof(int64_t) + 2 * sizeof(int32_t) + (size_t)cap * sizeof(int64_t);
+    const size_t need = 256 + (size_t)num_tiles * per_tile;
+    if (need > SEG_STATIC_BYTES) {
+        const long long max_n = (long long)((SEG_STATIC_BYTES - 256) / per_tile) * SEG_TILE;
+        return har::fail(HAR_E_UNSUPPORTED,
+                         "har_window_segments_static: %lld samples at window_len %d need %zu bytes of scratch but the "
+                         "built-in array holds %zu; the limit at this window_len is %lld samples - use "
+                         "har_window_segments, or split the stream at a bout boundary",
+                         (long long)n, window_len, need, SEG_STATIC_BYTES, max_n);
+    }
+    unsigned char* base = nullptr;
+    if (int rc = seg_static_base(&base)) return rc;
+    if (n == 0) return HAR_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    int64_t* total = reinterpret_cast<int64_t*>(base);
+    int64_t* first_b = reinterpret_cast<int64_t*>(base + 256);
+    int64_t* last_b = first_b + num_tiles;
+    int64_t* bstart_in = last_b + num_tiles;
+    int64_t* win_base = bstart_in + num_tiles;
+    int64_t* tile_wins = win_base + num_tiles;
+    int32_t* nlocal = reinterpret_cast<int32_t*>(tile_wins + num_tiles * cap);
+    int32_t* npre = nlocal + num_tiles;
+    int vec_ok = ((reinterpret_cast<uintptr_t>(d_user) | reinterpret_cast<uintptr_t>(d_activity)) & 15) == 0;
+    k_seg_tiles<<<(unsigned)num_tiles, SEG_THREADS, 0, s>>>(d_user, d_activity, d_ts, n, window_len, gap_ns, vec_ok,
+                                                            first_b, last_b, nlocal, tile_wins, cap);
+    HAR_LAUNCH_CHECK();
+    k_seg_scan<<<1, 1024, 0, s>>>(first_b, last_b, nlocal, num_tiles, n, window_len, bstart_in, npre, win_base, total);
+    HAR_LAUNCH_CHECK();
+    k_seg_emit<<<(unsigned)har::ceil_div(num_tiles, 128), 128, 0, s>>>(bstart_in, npre, nlocal, win_base, tile_wins, cap,
+                                                                       num_tiles, window_len, d_user, d_activity,
+                                                                       d_win_start, d_win_user, d_win_activity);
+    HAR_LAUNCH_CHECK();
+    int64_t h_total = 0;
+    HAR_CUDA(cudaMemcpyAsync(&h_total, total, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    HAR_CUDA(cudaStreamSynchronize(s));
+    *num_windows = h_total;
+    return HAR_OK;
+}
+
 HAR_API int har_window_features(const double* d_x, const double* d_y, const double* d_z, const int64_t* d_ts,
                                 int64_t n, const int64_t* d_win_start, int64_t num_windows, int32_t window_len,
                                 double* d_out, int64_t ld_out, har_stream_t stream) {

@@ -67,6 +67,26 @@ int har_window_segments(const int32_t* d_user, const int32_t* d_activity, const 
                         int64_t* d_win_start, int32_t* d_win_user, int32_t* d_win_activity,
                         int64_t* num_windows, har_stream_t stream);
 
+/* har_window_segments without any allocation — this entry point has no counterpart in the reference
+ * (or in Spark); it exists for hosts that are not allowed to allocate CUDA memory while running: a
+ * process whose device memory is entirely owned by another allocator, a fixed-latency loop, a plug-in
+ * sandbox limited to pre-approved buffers.  Same arguments and results as har_window_segments, but the
+ * per-tile scratch lives in a HAR_SEGMENTS_STATIC_BYTES array built into the library (held by every GPU
+ * that loads it, for the life of the process) instead of coming from cudaMallocAsync, and the call
+ * performs no cudaMalloc / cudaFree of any kind.
+ *   - size limit: 256 + ceil(n / 2048) * (40 + 8 * (2048 / window_len + 1)) bytes must fit the array,
+ *     i.e. 67,104,768 samples at window_len 200; larger inputs fail with HAR_E_UNSUPPORTED and a message
+ *     that states the limit.
+ *   - the first call on each device looks the array's address up; make that call at start-up, before
+ *     any stream capture.
+ *   - all calls on a device share the array: calls that can overlap on the GPU race and must be
+ *     serialised by the caller.  Stale contents from an earlier call are never read. */
+#define HAR_SEGMENTS_STATIC_BYTES (4u << 20)
+int har_window_segments_static(const int32_t* d_user, const int32_t* d_activity, const int64_t* d_ts,
+                               int64_t n, int32_t window_len, int64_t gap_ns,
+                               int64_t* d_win_start, int32_t* d_win_user, int32_t* d_win_activity,
+                               int64_t* num_windows, har_stream_t stream);
+
 /* a2 — per-window features: 43 doubles per window, row-major with leading dimension ld_out
  * (>= 43), column order HAR_NUM_WINDOW_FEATURES above.  *PEAK is NaN when the axis has fewer than
  * three local maxima ('?' in the reference CSV).  n = samples in d_x/d_y/d_z/d_ts; every window must
