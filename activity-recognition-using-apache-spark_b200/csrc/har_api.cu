@@ -20,6 +20,18 @@ int fail(int code, const char* fmt, ...) {
     return code;
 }
 
+void pool_setup() {
+    static bool done[64] = {false};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || done[dev]) return;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        unsigned long long thr = ~0ULL;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    done[dev] = true;
+}
+
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches += n; }
 long long launches_since_reset() { return g_launches.load(); }

@@ -47,6 +47,10 @@ void prof_resolve();
                              cudaGetErrorString(_e), __FILE__, __LINE__);                      \
     } while (0)
 
+// Keeps freed scratch cached in the device's default memory pool (release threshold = max) so that
+// repeated calls do not go back to the driver for every buffer.  Once per device.
+void pool_setup();
+
 // Stream-ordered scratch buffer (cudaMallocAsync); freed on the same stream.
 template <typename T>
 struct DevBuf {
@@ -62,6 +66,7 @@ struct DevBuf {
         s = stream;
         n = count;
         if (count == 0) return cudaSuccess;
+        pool_setup();
         return cudaMallocAsync((void**)&p, count * sizeof(T), stream);
     }
     void release() {

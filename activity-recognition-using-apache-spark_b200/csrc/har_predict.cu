@@ -102,16 +102,17 @@ int build_device_tables(har_forest* f, int is_forest, cudaStream_t s) {
     const int64_t N = (int64_t)f->feature.size();
     std::vector<PNode> pn((size_t)N);
     std::vector<double> leaf;
+    leaf.reserve((size_t)(N / 2 + T) * C);
     std::vector<int64_t> roots(T);
+    std::vector<std::pair<int64_t, int64_t>> q;      // BFS queue of (flat index, device index)
     int64_t next = 0, nleaf = 0;
     for (int t = 0; t < T; t++) {
         const int64_t base = f->tree_off[t];
         roots[t] = next++;
-        std::deque<std::pair<int64_t, int64_t>> q;      // (flat index, device index)
+        q.clear();
         q.emplace_back(base, roots[t]);
-        while (!q.empty()) {
-            auto [src, dst] = q.front();
-            q.pop_front();
+        for (size_t qi = 0; qi < q.size(); qi++) {
+            const int64_t src = q[qi].first, dst = q[qi].second;
             PNode& d = pn[(size_t)dst];
             if (f->feature[src] < 0) {
                 d.feature = -1; d.left = (int32_t)nleaf++; d.thr = 0.0;
@@ -140,9 +141,10 @@ int build_device_tables(har_forest* f, int is_forest, cudaStream_t s) {
             }
         }
     }
-    HAR_CUDA(cudaMalloc(&f->d_nodes, sizeof(PNode) * std::max<int64_t>(N, 1)));
-    HAR_CUDA(cudaMalloc((void**)&f->d_leaf, sizeof(double) * std::max<size_t>(leaf.size(), 1)));
-    HAR_CUDA(cudaMalloc((void**)&f->d_roots, sizeof(int64_t) * std::max(T, 1)));
+    har::pool_setup();
+    HAR_CUDA(cudaMallocAsync(&f->d_nodes, sizeof(PNode) * std::max<int64_t>(N, 1), s));
+    HAR_CUDA(cudaMallocAsync((void**)&f->d_leaf, sizeof(double) * std::max<size_t>(leaf.size(), 1), s));
+    HAR_CUDA(cudaMallocAsync((void**)&f->d_roots, sizeof(int64_t) * std::max(T, 1), s));
     HAR_CUDA(cudaMemcpyAsync(f->d_nodes, pn.data(), sizeof(PNode) * N, cudaMemcpyHostToDevice, s));
     HAR_CUDA(cudaMemcpyAsync(f->d_leaf, leaf.data(), sizeof(double) * leaf.size(), cudaMemcpyHostToDevice, s));
     HAR_CUDA(cudaMemcpyAsync(f->d_roots, roots.data(), sizeof(int64_t) * T, cudaMemcpyHostToDevice, s));

@@ -7,8 +7,11 @@
 // groups, feature-subset draws, child creation, pruning) follows SURVEY.md A.5-A.9 on the host, as it
 // does on Spark's driver; everything that touches rows runs in the kernels of har_tree_kernels.cuh.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <memory>
+#include <thread>
 
 #include "har_forest.h"
 #include "har_tree_kernels.cuh"
@@ -275,7 +278,7 @@ struct LNode {
     int feature = -1, kind = 0, split = 0, arity = 0;
     double threshold = 0, gain = 0, impurity = 0;
     uint64_t mask = 0;
-    std::vector<double> stats;
+    uint32_t stats[HAR_MAX_CLASSES] = {0};     // class counts (integers < 2^32)
     int left = -1, right = -1;
     // rows of this rank at the node
     int64_t start = 0;
@@ -284,8 +287,8 @@ struct LNode {
     std::vector<int32_t> subset;
 };
 int level_of(int id) { int l = 0; while (id > 1) { id >>= 1; l++; } return l; }
-int first_argmax(const double* s, int C) {
-    int b = -1; double mv = 0;
+int first_argmax(const uint32_t* s, int C) {
+    int b = -1; uint32_t mv = 0;
     for (int c = 0; c < C; c++) if (b < 0 || s[c] > mv) { b = c; mv = s[c]; }
     return b;
 }
@@ -297,9 +300,9 @@ int64_t emit_node(har_forest& fo, const std::vector<LNode>& tree, int idx, int64
     const int64_t me = (int64_t)fo.feature.size();
     fo.feature.push_back(-1); fo.left.push_back(-1); fo.right.push_back(-1); fo.node_id.push_back(n.id);
     fo.arity.push_back(0); fo.threshold.push_back(0.0); fo.left_mask.push_back(0);
-    fo.prediction.push_back((double)first_argmax(n.stats.data(), C));
+    fo.prediction.push_back((double)first_argmax(n.stats, C));
     fo.impurity.push_back(0.0); fo.gain.push_back(0.0);
-    fo.stats.insert(fo.stats.end(), n.stats.begin(), n.stats.end());
+    for (int c = 0; c < C; c++) fo.stats.push_back((double)n.stats[c]);
     if (n.left >= 0) {
         bool ll = false, rl = false;
         int64_t li = emit_node(fo, tree, n.left, base, &ll);
@@ -339,6 +342,19 @@ struct Pinned {
 };
 
 struct GroupItem { int tree; int node; };
+
+// Small fork-join helper for the host-side (driver) work; `go` = false runs inline.
+template <typename Fn>
+void parallel_for(int n, bool go, Fn fn) {
+    unsigned hw = std::thread::hardware_concurrency();
+    int nt = (int)std::min<unsigned>(hw ? hw : 1, 8);
+    if (!go || nt <= 1 || n < 2) { for (int i = 0; i < n; i++) fn(i); return; }
+    nt = std::min(nt, n);
+    std::vector<std::thread> th;
+    th.reserve(nt);
+    for (int k = 0; k < nt; k++) th.emplace_back([=, &fn] { for (int i = k; i < n; i += nt) fn(i); });
+    for (auto& t : th) t.join();
+}
 
 }  // namespace
 
@@ -433,6 +449,12 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     if (!part_off) { part_off = po_default; num_parts = 1; }
     const int part_offset = dist ? dist->partition_offset : 0;
     const long long launches0 = launches_since_reset();
+    // HAR_FIT_TRACE=1: wall-clock split of the fit (stderr), for tuning only
+    const bool trace = std::getenv("HAR_FIT_TRACE") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms_since = [&](std::chrono::steady_clock::time_point a) { return std::chrono::duration<double, std::milli>(now() - a).count(); };
+    double t_prep = 0, t_wait = 0, t_post = 0;
+    auto t_begin = now();
 
     Meta m;
     if (int rc = build_meta(m, F, C, n_global, MB, arity)) return rc;
@@ -517,7 +539,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     std::vector<std::vector<LNode>> trees(T);
     std::vector<GroupItem> stack;
     for (int t = 0; t < T; t++) {
-        LNode r; r.id = 1; r.stats.assign(C, 0.0); r.start = 0; r.count = root_cnt[t]; r.buf = 0;
+        LNode r; r.id = 1; r.start = 0; r.count = root_cnt[t]; r.buf = 0;
+        trees[t].reserve(256);
         trees[t].push_back(r);
         stack.push_back({t, 0});
     }
@@ -529,7 +552,10 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     DevBuf<NodeDesc> d_nodes;
     DevBuf<NodeResult> d_res;
     DevBuf<int32_t> d_item_off, d_chunk_left;
-    Pinned<NodeDesc> h_nodes; Pinned<NodeResult> h_res; Pinned<int32_t> h_item_off, h_sub;
+    // page-locked staging, kept across fits (cudaMallocHost is far too slow to repeat per call)
+    static thread_local Pinned<NodeDesc> h_nodes;
+    static thread_local Pinned<NodeResult> h_res;
+    static thread_local Pinned<int32_t> h_item_off, h_sub;
     size_t cap_nodes = 0, cap_hist = 0, cap_items = 0, cap_sub = 0;
     if (!subsample) {
         HAR_CUDA(d_loff_all.alloc(F + 1, s));
@@ -544,7 +570,10 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
 
     std::vector<GroupItem> group;
     std::vector<NodeResult> group_res;
+    if (trace) cudaStreamSynchronize(s);
+    const double t_setup = ms_since(t_begin);
     while (!stack.empty()) {
+        auto t_a = now();
         // ---- selectNodesToSplit ----
         group.clear();
         int64_t mem = 0;
@@ -667,66 +696,111 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 prof_end(PROF_PART_SCATTER, s, (double)rows_total);
             }
             HAR_CUDA(cudaMemcpyAsync(h_res.p, d_res.p, sizeof(NodeResult) * ng, cudaMemcpyDeviceToHost, s));
+            t_prep += ms_since(t_a);
+            t_a = now();
             HAR_CUDA(cudaStreamSynchronize(s));
+            t_wait += ms_since(t_a);
+            t_a = now();
             std::copy(h_res.p, h_res.p + ng, group_res.begin() + g0);
             g0 = g1;
         }
 
         // ---- driver side of findBestSplits: children, leaf rules, stack pushes ----
+        // Trees are independent, so they are processed by a few host threads; the pushes are then appended
+        // in the order Spark's `nodesForGroup.foreach` would produce (Scala mutable.HashMap order of the tree
+        // indices, pop order inside a tree).
         std::vector<int> tkeys;
         {
             std::vector<char> seen(T, 0);
             for (auto& gi : group) if (!seen[gi.tree]) { seen[gi.tree] = 1; tkeys.push_back(gi.tree); }
         }
         std::vector<int> torder = scala_hashmap_order(tkeys);
-        std::vector<std::vector<int>> by_tree(T);
+        std::vector<std::vector<int>> by_tree(T), pushes(T);
         for (int g = 0; g < (int)ng_total; g++) by_tree[group[g].tree].push_back(g);
-        for (int oi : torder) {
-            const int t = tkeys[oi];
+        auto process_tree = [&](int t) {
+            std::vector<LNode>& tr = trees[t];
+            tr.reserve(tr.size() + 2 * by_tree[t].size());
             for (int g : by_tree[t]) {
                 const NodeResult& r = group_res[g];
                 const int ni = group[g].node;
-                const int level = level_of(trees[t][ni].id);
+                const int level = level_of(tr[ni].id);
                 const bool is_leaf = !(r.gain > 0.0) || level == p->max_depth;
                 {
-                    LNode& nd = trees[t][ni];
+                    LNode& nd = tr[ni];
                     nd.is_leaf = is_leaf; nd.valid = r.valid != 0; nd.gain = r.gain; nd.impurity = r.impurity;
-                    for (int c = 0; c < C; c++) nd.stats[c] = (double)r.parent[c];
-                    std::vector<int32_t>().swap(nd.subset);
+                    for (int c = 0; c < C; c++) nd.stats[c] = r.parent[c];
+                    if (!nd.subset.empty()) std::vector<int32_t>().swap(nd.subset);
                 }
                 if (is_leaf) continue;
                 const bool child_leaf = level + 1 == p->max_depth;
                 const bool ll = child_leaf || r.left_imp == 0.0, rl = child_leaf || r.right_imp == 0.0;
                 const bool parted = !(ll && rl);
-                LNode L, R;
-                L.id = trees[t][ni].id * 2; R.id = L.id + 1;
+                const int li = (int)tr.size();
+                tr.emplace_back(); tr.emplace_back();
+                LNode& nd = tr[ni];
+                LNode& L = tr[li]; LNode& R = tr[li + 1];
+                L.id = nd.id * 2; R.id = L.id + 1;
                 L.is_leaf = ll; R.is_leaf = rl; L.impurity = r.left_imp; R.impurity = r.right_imp;
-                L.stats.resize(C); R.stats.resize(C);
-                for (int c = 0; c < C; c++) { L.stats[c] = (double)r.left[c]; R.stats[c] = (double)r.right[c]; }
-                const LNode& pn = trees[t][ni];
-                L.start = pn.start; L.count = parted ? r.n_left : 0; L.buf = pn.buf ^ 1;
-                R.start = pn.start + L.count; R.count = parted ? pn.count - r.n_left : 0; R.buf = pn.buf ^ 1;
-                const int li = (int)trees[t].size();
-                trees[t].push_back(L); trees[t].push_back(R);
-                LNode& nd = trees[t][ni];
+                for (int c = 0; c < C; c++) { L.stats[c] = r.left[c]; R.stats[c] = r.right[c]; }
+                L.start = nd.start; L.count = parted ? r.n_left : 0; L.buf = nd.buf ^ 1;
+                R.start = nd.start + L.count; R.count = parted ? nd.count - r.n_left : 0; R.buf = nd.buf ^ 1;
                 nd.left = li; nd.right = li + 1;
                 nd.feature = r.feature; nd.kind = r.kind; nd.split = r.split; nd.mask = r.left_mask; nd.arity = m.arity[r.feature];
                 nd.threshold = r.kind == KIND_CONT ? fo->thresholds[(size_t)r.feature * MB + r.split] : 0.0;
-                if (!ll) stack.push_back({t, li});
-                if (!rl) stack.push_back({t, li + 1});
+                if (!ll) pushes[t].push_back(li);
+                if (!rl) pushes[t].push_back(li + 1);
             }
+        };
+        parallel_for((int)tkeys.size(), ng_total >= 512, [&](int k) { process_tree(tkeys[k]); });
+        for (int oi : torder) {
+            const int t = tkeys[oi];
+            for (int ni : pushes[t]) stack.push_back({t, ni});
         }
+        t_post += ms_since(t_a);
     }
+    auto t_emit = now();
 
-    // ---- toNode(prune = true) ----
+    // ---- toNode(prune = true): per tree in parallel, then concatenated in tree order ----
     fo->tree_off.assign(T + 1, 0);
-    for (int t = 0; t < T; t++) {
-        bool leaf = false;
-        fo->tree_off[t] = (int64_t)fo->feature.size();
-        emit_node(*fo, trees[t], 0, fo->tree_off[t], &leaf);
+    {
+        std::vector<har_forest> parts(T);
+        parallel_for(T, true, [&](int t) {
+            har_forest& pf = parts[t];
+            pf.C = C;
+            const size_t nn = trees[t].size();
+            pf.feature.reserve(nn); pf.left.reserve(nn); pf.right.reserve(nn); pf.node_id.reserve(nn); pf.arity.reserve(nn);
+            pf.threshold.reserve(nn); pf.left_mask.reserve(nn); pf.prediction.reserve(nn); pf.impurity.reserve(nn);
+            pf.gain.reserve(nn); pf.stats.reserve(nn * C);
+            bool leaf = false;
+            emit_node(pf, trees[t], 0, 0, &leaf);
+        });
+        size_t total_nodes = 0;
+        for (int t = 0; t < T; t++) { fo->tree_off[t] = (int64_t)total_nodes; total_nodes += parts[t].feature.size(); }
+        fo->feature.reserve(total_nodes); fo->left.reserve(total_nodes); fo->right.reserve(total_nodes);
+        fo->node_id.reserve(total_nodes); fo->arity.reserve(total_nodes); fo->threshold.reserve(total_nodes);
+        fo->left_mask.reserve(total_nodes); fo->prediction.reserve(total_nodes); fo->impurity.reserve(total_nodes);
+        fo->gain.reserve(total_nodes); fo->stats.reserve(total_nodes * C);
+        for (int t = 0; t < T; t++) {
+            const har_forest& pf = parts[t];
+            fo->feature.insert(fo->feature.end(), pf.feature.begin(), pf.feature.end());
+            fo->left.insert(fo->left.end(), pf.left.begin(), pf.left.end());
+            fo->right.insert(fo->right.end(), pf.right.begin(), pf.right.end());
+            fo->node_id.insert(fo->node_id.end(), pf.node_id.begin(), pf.node_id.end());
+            fo->arity.insert(fo->arity.end(), pf.arity.begin(), pf.arity.end());
+            fo->threshold.insert(fo->threshold.end(), pf.threshold.begin(), pf.threshold.end());
+            fo->left_mask.insert(fo->left_mask.end(), pf.left_mask.begin(), pf.left_mask.end());
+            fo->prediction.insert(fo->prediction.end(), pf.prediction.begin(), pf.prediction.end());
+            fo->impurity.insert(fo->impurity.end(), pf.impurity.begin(), pf.impurity.end());
+            fo->gain.insert(fo->gain.end(), pf.gain.begin(), pf.gain.end());
+            fo->stats.insert(fo->stats.end(), pf.stats.begin(), pf.stats.end());
+        }
     }
     fo->tree_off[T] = (int64_t)fo->feature.size();
     fo->num_launches = launches_since_reset() - launches0;
+    if (trace)
+        fprintf(stderr, "[har_forest_fit] setup %.2f ms | loop: host prep+launch %.2f, gpu wait %.2f, driver-side %.2f | toNode %.2f | "
+                        "total %.2f ms, %lld groups, %lld batches, %zu nodes\n", t_setup, t_prep, t_wait, t_post, ms_since(t_emit),
+                ms_since(t_begin), (long long)fo->num_groups, (long long)fo->num_batches, fo->feature.size());
     (void)world;
     *out = fo.release();
     return HAR_OK;

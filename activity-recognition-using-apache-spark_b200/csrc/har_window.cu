@@ -15,6 +15,9 @@
 //       from HBM exactly once; reductions are warp shuffles in fp64 with a fixed butterfly order.
 #include "har_common.cuh"
 
+#include <algorithm>
+#include <cstdlib>
+
 namespace {
 
 constexpr int SEG_THREADS = 256;
@@ -416,6 +419,8 @@ k_window_features(const double* __restrict__ x, const double* __restrict__ y, co
     }
 }
 
+#include "har_window_v2.cuh"
+
 }  // namespace
 
 HAR_API int har_window_segments(const int32_t* d_user, const int32_t* d_activity, const int64_t* d_ts,
@@ -559,6 +564,21 @@ HAR_API int har_window_features(const double* d_x, const double* d_y, const doub
     if (ld_out < HAR_NUM_WINDOW_FEATURES) return har::fail(HAR_E_INVALID, "har_window_features: ld_out < 43");
     if (num_windows <= 0) return HAR_OK;
     cudaStream_t s = (cudaStream_t)stream;
+    static const bool use_tma_kernel = std::getenv("HAR_WINDOW_KERNEL") && std::string(std::getenv("HAR_WINDOW_KERNEL")) == "tma";
+    if (!use_tma_kernel) {
+        // register-resident kernel: 2 windows per warp, 4 warps per CTA, grid = a few CTAs per SM (persistent loop)
+        const int64_t pairs = har::ceil_div(num_windows, 2);
+        int64_t blocks = std::min<int64_t>(har::ceil_div(pairs, 4), (int64_t)har::kNumSMs * 3 * 8);
+        const int kiter = (window_len + 15) / 16;
+        har::prof_begin(s);
+        if (kiter <= 13)
+            k_window_features_v2<13><<<(unsigned)blocks, 128, 0, s>>>(d_x, d_y, d_z, d_ts, d_win_start, num_windows, window_len, d_out, ld_out);
+        else
+            k_window_features_v2<16><<<(unsigned)blocks, 128, 0, s>>>(d_x, d_y, d_z, d_ts, d_win_start, num_windows, window_len, d_out, ld_out);
+        HAR_LAUNCH_CHECK();
+        har::prof_end(har::PROF_WINDOW_FEATURES, s, (double)num_windows * window_len);
+        return HAR_OK;
+    }
     const int stride = (window_len + 3) & ~1;
     const size_t per_warp = ((size_t)WF_STAGES * 3 * stride + 44) * sizeof(double) + WF_STAGES * sizeof(uint64_t);
     const size_t smem = per_warp * WF_WARPS;

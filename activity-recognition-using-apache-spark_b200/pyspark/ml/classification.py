@@ -120,20 +120,23 @@ class _TreeEstimatorBase(Estimator, _TreeClassifierParams):
 
 
 class DecisionTreeClassifier(_TreeEstimatorBase):
-    def __init__(self, featuresCol="features", labelCol="label", predictionCol="prediction",
-                 probabilityCol="probability", rawPredictionCol="rawPrediction", maxDepth=5, maxBins=32,
-                 minInstancesPerNode=1, minInfoGain=0.0, maxMemoryInMB=256, cacheNodeIds=False,
-                 checkpointInterval=10, impurity="gini", seed=None, thresholds=None):
+    """DecisionTreeClassifier(featuresCol="features", labelCol="label", predictionCol="prediction",
+    probabilityCol="probability", rawPredictionCol="rawPrediction", maxDepth=5, maxBins=32,
+    minInstancesPerNode=1, minInfoGain=0.0, maxMemoryInMB=256, cacheNodeIds=False, checkpointInterval=10,
+    impurity="gini", seed=None) — keyword arguments only, as in pyspark; only what is passed is `set`."""
+    _KW = tuple(_TREE_PARAM_NAMES)
+
+    def __init__(self, *args, **kwargs):
         super().__init__()
         self._tree_defaults()
-        kw = dict(featuresCol=featuresCol, labelCol=labelCol, predictionCol=predictionCol,
-                  probabilityCol=probabilityCol, rawPredictionCol=rawPredictionCol, maxDepth=maxDepth,
-                  maxBins=maxBins, minInstancesPerNode=minInstancesPerNode, minInfoGain=minInfoGain,
-                  maxMemoryInMB=maxMemoryInMB, cacheNodeIds=cacheNodeIds, checkpointInterval=checkpointInterval,
-                  impurity=impurity, seed=seed, thresholds=thresholds)
-        self.setParams(**kw)
+        if args:
+            raise TypeError("Method __init__ forces keyword arguments.")
+        self.setParams(**kwargs)
 
     def setParams(self, **kw):
+        for k in kw:
+            if k not in self._KW:
+                raise TypeError("__init__() got an unexpected keyword argument '%s'" % k)
         return self._set(**{k: v for k, v in kw.items() if v is not None})
 
     def _fit(self, dataset):
@@ -271,23 +274,22 @@ class RandomForestClassifier(_TreeEstimatorBase):
     subsamplingRate = Param(Params._dummy_parent, "subsamplingRate", "Fraction of the training data used for learning "
                             "each decision tree, in range (0, 1].", TypeConverters.toFloat)
 
-    def __init__(self, featuresCol="features", labelCol="label", predictionCol="prediction",
-                 probabilityCol="probability", rawPredictionCol="rawPrediction", maxDepth=5, maxBins=32,
-                 minInstancesPerNode=1, minInfoGain=0.0, maxMemoryInMB=256, cacheNodeIds=False,
-                 checkpointInterval=10, impurity="gini", numTrees=20, featureSubsetStrategy="auto", seed=None,
-                 subsamplingRate=1.0, thresholds=None):
+    _KW = tuple(_TREE_PARAM_NAMES) + ("numTrees", "featureSubsetStrategy", "subsamplingRate")
+
+    def __init__(self, *args, **kwargs):
         super().__init__()
         self._tree_defaults()
         self._setDefault(numTrees=20, featureSubsetStrategy="auto", subsamplingRate=1.0)
-        kw = dict(featuresCol=featuresCol, labelCol=labelCol, predictionCol=predictionCol,
-                  probabilityCol=probabilityCol, rawPredictionCol=rawPredictionCol, maxDepth=maxDepth,
-                  maxBins=maxBins, minInstancesPerNode=minInstancesPerNode, minInfoGain=minInfoGain,
-                  maxMemoryInMB=maxMemoryInMB, cacheNodeIds=cacheNodeIds, checkpointInterval=checkpointInterval,
-                  impurity=impurity, numTrees=numTrees, featureSubsetStrategy=str(featureSubsetStrategy), seed=seed,
-                  subsamplingRate=subsamplingRate, thresholds=thresholds)
-        self.setParams(**kw)
+        if args:
+            raise TypeError("Method __init__ forces keyword arguments.")
+        self.setParams(**kwargs)
 
     def setParams(self, **kw):
+        for k in kw:
+            if k not in self._KW:
+                raise TypeError("__init__() got an unexpected keyword argument '%s'" % k)
+        if "featureSubsetStrategy" in kw and kw["featureSubsetStrategy"] is not None:
+            kw["featureSubsetStrategy"] = str(kw["featureSubsetStrategy"])
         return self._set(**{k: v for k, v in kw.items() if v is not None})
 
     def _fit(self, dataset):
