@@ -278,7 +278,6 @@ struct LNode {
     int feature = -1, kind = 0, split = 0, arity = 0;
     double threshold = 0, gain = 0, impurity = 0;
     uint64_t mask = 0;
-    uint32_t stats[HAR_MAX_CLASSES] = {0};     // class counts (integers < 2^32)
     int left = -1, right = -1;
     // rows of this rank at the node
     int64_t start = 0;
@@ -294,19 +293,21 @@ int first_argmax(const uint32_t* s, int C) {
 }
 
 // LearningNode.toNode(prune = true) into the flat pre-order layout
-int64_t emit_node(har_forest& fo, const std::vector<LNode>& tree, int idx, int64_t base, bool* is_leaf_out) {
+int64_t emit_node(har_forest& fo, const std::vector<LNode>& tree, const std::vector<uint32_t>& tstats, int idx, int64_t base,
+                  bool* is_leaf_out) {
     const LNode& n = tree[idx];
     const int C = fo.C;
     const int64_t me = (int64_t)fo.feature.size();
     fo.feature.push_back(-1); fo.left.push_back(-1); fo.right.push_back(-1); fo.node_id.push_back(n.id);
     fo.arity.push_back(0); fo.threshold.push_back(0.0); fo.left_mask.push_back(0);
-    fo.prediction.push_back((double)first_argmax(n.stats, C));
+    const uint32_t* nstats = tstats.data() + (size_t)idx * C;
+    fo.prediction.push_back((double)first_argmax(nstats, C));
     fo.impurity.push_back(0.0); fo.gain.push_back(0.0);
-    for (int c = 0; c < C; c++) fo.stats.push_back((double)n.stats[c]);
+    for (int c = 0; c < C; c++) fo.stats.push_back((double)nstats[c]);
     if (n.left >= 0) {
         bool ll = false, rl = false;
-        int64_t li = emit_node(fo, tree, n.left, base, &ll);
-        int64_t ri = emit_node(fo, tree, n.right, base, &rl);
+        int64_t li = emit_node(fo, tree, tstats, n.left, base, &ll);
+        int64_t ri = emit_node(fo, tree, tstats, n.right, base, &rl);
         if (ll && rl && fo.prediction[base + li] == fo.prediction[base + ri]) {
             const size_t keep = (size_t)me + 1;
             fo.feature.resize(keep); fo.left.resize(keep); fo.right.resize(keep); fo.node_id.resize(keep);
@@ -408,7 +409,7 @@ HAR_API int har_node_histogram(const uint8_t* d_bins, int64_t ldb, const uint8_t
     HAR_CUDA(cudaMemcpyAsync(d_io.p, item_off, sizeof item_off, cudaMemcpyHostToDevice, s));
     HAR_CUDA(cudaMemcpyAsync(d_loff.p, loff.data(), sizeof(int32_t) * (F + 1), cudaMemcpyHostToDevice, s));
     HAR_CUDA(cudaMemsetAsync(d_kind.p, KIND_CONT, F, s));
-    const size_t smem = (HIST_TILE_WORDS + 32) * sizeof(uint32_t);
+    const size_t smem = (HIST_TILE_WORDS + 32 + HIST_FTAB) * sizeof(uint32_t);
     const bool vec = (ldb % 16 == 0) && ((reinterpret_cast<uintptr_t>(d_bins) & 15) == 0);
     if (vec) {
         HAR_CUDA(cudaFuncSetAttribute(k_node_hist<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -487,6 +488,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     const int64_t ldb = (F + 15) & ~15;
     DevBuf<uint8_t> d_bins;
     HAR_CUDA(d_bins.alloc((size_t)std::max<int64_t>(n, 1) * ldb, s));
+    if (ldb != F) HAR_CUDA(cudaMemsetAsync(d_bins.p, 0, (size_t)std::max<int64_t>(n, 1) * ldb, s));   // zero padding bytes
     if (int rc = bin_features_impl(d_X, n, F, ld, arity, fo->thresholds.data(), fo->nsplits.data(), MB, d_bins.p, ldb, s)) return rc;
 
     // bagging weights
@@ -537,17 +539,20 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
 
     // trees + node stack (RandomForest.run)
     std::vector<std::vector<LNode>> trees(T);
+    std::vector<std::vector<uint32_t>> tree_stats(T);      // [node][C] class counts, kept out of the hot LNode
     std::vector<GroupItem> stack;
     for (int t = 0; t < T; t++) {
         LNode r; r.id = 1; r.start = 0; r.count = root_cnt[t]; r.buf = 0;
         trees[t].reserve(256);
         trees[t].push_back(r);
+        tree_stats[t].assign(C, 0);
         stack.push_back({t, 0});
     }
     JavaRand rng(p->seed);
 
     // batch buffers
-    const int64_t budget_words = 96LL << 20;                 // 384 MB of counters per device batch
+    int64_t budget_words = 96LL << 20;                       // 384 MB of counters per device batch
+    if (const char* e = std::getenv("HAR_HIST_BUDGET_WORDS")) budget_words = std::max<int64_t>(1, std::atoll(e));   // tests
     DevBuf<uint32_t> d_hist;
     DevBuf<NodeDesc> d_nodes;
     DevBuf<NodeResult> d_res;
@@ -561,7 +566,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_CUDA(d_loff_all.alloc(F + 1, s));
         HAR_CUDA(cudaMemcpyAsync(d_loff_all.p, m.loff.data(), sizeof(int32_t) * (F + 1), cudaMemcpyHostToDevice, s));
     }
-    const size_t hist_smem = (HIST_TILE_WORDS + 32) * sizeof(uint32_t);
+    const size_t hist_smem = (HIST_TILE_WORDS + 32 + HIST_FTAB) * sizeof(uint32_t);
     HAR_CUDA(cudaFuncSetAttribute(k_node_hist<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem));
     HAR_CUDA(cudaFuncSetAttribute(k_node_hist<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem));
     const size_t bs_smem = ((size_t)BS_ROWS * (C + 1) + 64 * C) * 4 * (BS_THREADS / 32) + MAX_CAT * (BS_THREADS / 32) * 12 + 128 +
@@ -597,7 +602,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         }
         fo->num_groups++;
         const int64_t ng_total = (int64_t)group.size();
-        group_res.resize(ng_total);
+        const NodeResult* res_ptr = nullptr;
 
         // ---- findBestSplits, in device batches bounded by the counter budget ----
         int64_t g0 = 0;
@@ -701,7 +706,12 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             HAR_CUDA(cudaStreamSynchronize(s));
             t_wait += ms_since(t_a);
             t_a = now();
-            std::copy(h_res.p, h_res.p + ng, group_res.begin() + g0);
+            if (ng == ng_total) res_ptr = h_res.p;                 // whole group in one batch: read the staging buffer in place
+            else {
+                if ((int64_t)group_res.size() < ng_total) group_res.resize(ng_total);
+                std::copy(h_res.p, h_res.p + ng, group_res.begin() + g0);
+                res_ptr = group_res.data();
+            }
             g0 = g1;
         }
 
@@ -719,16 +729,18 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         for (int g = 0; g < (int)ng_total; g++) by_tree[group[g].tree].push_back(g);
         auto process_tree = [&](int t) {
             std::vector<LNode>& tr = trees[t];
+            std::vector<uint32_t>& ts = tree_stats[t];
             tr.reserve(tr.size() + 2 * by_tree[t].size());
+            ts.reserve((tr.size() + 2 * by_tree[t].size()) * C);
             for (int g : by_tree[t]) {
-                const NodeResult& r = group_res[g];
+                const NodeResult& r = res_ptr[g];
                 const int ni = group[g].node;
                 const int level = level_of(tr[ni].id);
                 const bool is_leaf = !(r.gain > 0.0) || level == p->max_depth;
                 {
                     LNode& nd = tr[ni];
                     nd.is_leaf = is_leaf; nd.valid = r.valid != 0; nd.gain = r.gain; nd.impurity = r.impurity;
-                    for (int c = 0; c < C; c++) nd.stats[c] = r.parent[c];
+                    for (int c = 0; c < C; c++) ts[(size_t)ni * C + c] = r.parent[c];
                     if (!nd.subset.empty()) std::vector<int32_t>().swap(nd.subset);
                 }
                 if (is_leaf) continue;
@@ -741,7 +753,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 LNode& L = tr[li]; LNode& R = tr[li + 1];
                 L.id = nd.id * 2; R.id = L.id + 1;
                 L.is_leaf = ll; R.is_leaf = rl; L.impurity = r.left_imp; R.impurity = r.right_imp;
-                for (int c = 0; c < C; c++) { L.stats[c] = r.left[c]; R.stats[c] = r.right[c]; }
+                ts.resize((size_t)(li + 2) * C);
+                for (int c = 0; c < C; c++) { ts[(size_t)li * C + c] = r.left[c]; ts[(size_t)(li + 1) * C + c] = r.right[c]; }
                 L.start = nd.start; L.count = parted ? r.n_left : 0; L.buf = nd.buf ^ 1;
                 R.start = nd.start + L.count; R.count = parted ? nd.count - r.n_left : 0; R.buf = nd.buf ^ 1;
                 nd.left = li; nd.right = li + 1;
@@ -772,7 +785,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             pf.threshold.reserve(nn); pf.left_mask.reserve(nn); pf.prediction.reserve(nn); pf.impurity.reserve(nn);
             pf.gain.reserve(nn); pf.stats.reserve(nn * C);
             bool leaf = false;
-            emit_node(pf, trees[t], 0, 0, &leaf);
+            emit_node(pf, trees[t], tree_stats[t], 0, 0, &leaf);
         });
         size_t total_nodes = 0;
         for (int t = 0; t < T; t++) { fo->tree_off[t] = (int64_t)total_nodes; total_nodes += parts[t].feature.size(); }

@@ -146,6 +146,20 @@ def test_forest_on_synthetic_identical_to_oracle(kw):
     assert np.array_equal(_bits(raw), _bits(ro)) and np.array_equal(_bits(prob), _bits(po_)) and np.array_equal(pred, pr)
 
 
+def test_node_group_split_into_several_device_batches(monkeypatch):
+    """A Spark node group larger than the device counter budget is processed in several batches; results
+    must not depend on the batching."""
+    from har_b200 import core
+    X, y, arity = synth_tree_data(12000, F=20, C=4, seed=3)
+    ref = core.fit_forest(X, y, num_classes=4, num_trees=8, max_depth=7, feature_subset="all", seed=6)
+    monkeypatch.setenv("HAR_HIST_BUDGET_WORDS", "40000")          # ~15 nodes per batch
+    g = core.fit_forest(X, y, num_classes=4, num_trees=8, max_depth=7, feature_subset="all", seed=6)
+    o = orc.fit_forest(X, y, num_classes=4, num_trees=8, max_depth=7, feature_subset="all", seed=6)
+    assert g.num_batches > 4 * ref.num_batches and g.num_groups == ref.num_groups == o.num_groups
+    assert_forest_equal(o, g)
+    assert_forest_equal(ref, g)
+
+
 def test_entropy_forest_same_structure():
     """Entropy uses log(); CUDA's and glibc's may differ in the last ulp, so gains are compared to 1e-12
     and the structure must still be identical on this data (documented caveat in DESIGN.md)."""
