@@ -420,6 +420,7 @@ k_window_features(const double* __restrict__ x, const double* __restrict__ y, co
 }
 
 #include "har_window_v2.cuh"
+#include "har_window_v3.cuh"
 
 }  // namespace
 
@@ -564,9 +565,25 @@ HAR_API int har_window_features(const double* d_x, const double* d_y, const doub
     if (ld_out < HAR_NUM_WINDOW_FEATURES) return har::fail(HAR_E_INVALID, "har_window_features: ld_out < 43");
     if (num_windows <= 0) return HAR_OK;
     cudaStream_t s = (cudaStream_t)stream;
-    static const bool use_tma_kernel = std::getenv("HAR_WINDOW_KERNEL") && std::string(std::getenv("HAR_WINDOW_KERNEL")) == "tma";
-    if (!use_tma_kernel) {
-        // register-resident kernel: 2 windows per warp, 4 warps per CTA, grid = a few CTAs per SM (persistent loop)
+    // HAR_WINDOW_KERNEL = v3 (default; 8 lanes/window, register resident, compact code) | v2 (16 lanes/window,
+    // unrolled over axes) | tma (first version: one warp per window, cp.async.bulk staging) - kept for A/B timing
+    const char* sel = std::getenv("HAR_WINDOW_KERNEL");
+    const std::string which = sel ? sel : "v3";
+    if (which == "v3") {
+        const int64_t quads = har::ceil_div(num_windows, 4);
+        const unsigned blocks = (unsigned)std::min<int64_t>(har::ceil_div(quads, 4), (int64_t)har::kNumSMs * 3 * 8);
+        har::prof_begin(s);
+        if (window_len == 200)
+            k_window_features_v3<25, true><<<blocks, 128, 0, s>>>(d_x, d_y, d_z, d_ts, d_win_start, num_windows, window_len, d_out, ld_out);
+        else if (window_len <= 128)
+            k_window_features_v3<16, false><<<blocks, 128, 0, s>>>(d_x, d_y, d_z, d_ts, d_win_start, num_windows, window_len, d_out, ld_out);
+        else
+            k_window_features_v3<32, false><<<blocks, 128, 0, s>>>(d_x, d_y, d_z, d_ts, d_win_start, num_windows, window_len, d_out, ld_out);
+        HAR_LAUNCH_CHECK();
+        har::prof_end(har::PROF_WINDOW_FEATURES, s, (double)num_windows * window_len);
+        return HAR_OK;
+    }
+    if (which == "v2") {
         const int64_t pairs = har::ceil_div(num_windows, 2);
         int64_t blocks = std::min<int64_t>(har::ceil_div(pairs, 4), (int64_t)har::kNumSMs * 3 * 8);
         const int kiter = (window_len + 15) / 16;
