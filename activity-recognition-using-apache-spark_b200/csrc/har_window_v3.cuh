@@ -8,7 +8,7 @@
 __device__ __noinline__ double precise_sqrt(double s) { return sqrt(s); }
 
 template <int KITER, bool EXACT>       // EXACT: L == 8 * KITER (no bounds checks)
-__global__ void __launch_bounds__(128, 3)
+__global__ void __launch_bounds__(128, 4)
 k_window_features_v3(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z,
                      const int64_t* __restrict__ ts, const int64_t* __restrict__ win_start, int64_t nw, int L,
                      double* __restrict__ out, int64_t ld_out) {
@@ -19,6 +19,8 @@ k_window_features_v3(const double* __restrict__ x, const double* __restrict__ y,
     const double dL = (double)L;
     const double qnan = __longlong_as_double(0x7ff8000000000000LL);
     __shared__ unsigned s_bins[4][4][10];                  // [warp][window of the warp][bin]
+    __shared__ double s_r2[KITER][128];                    // per-thread running x^2+y^2+z^2 (frees KITER*2 registers)
+    double* r2 = &s_r2[0][threadIdx.x];                    // element k at r2[k * 128]: conflict-free
     unsigned* bins_w = s_bins[threadIdx.x >> 5][grp];
     const unsigned gmask = 0xffu << (grp * G);
 
@@ -27,9 +29,6 @@ k_window_features_v3(const double* __restrict__ x, const double* __restrict__ y,
         const bool live = w < nw;
         const int64_t st = win_start[live ? w : nw - 1];
         double* dst = out + (live ? w : nw - 1) * ld_out;
-        double r2[KITER];
-#pragma unroll
-        for (int k = 0; k < KITER; k++) r2[k] = 0.0;
 
 #pragma unroll 1
         for (int a = 0; a < 3; a++) {
@@ -43,7 +42,7 @@ k_window_features_v3(const double* __restrict__ x, const double* __restrict__ y,
             for (int k = 0; k < KITER; k++) {
                 if (EXACT || sub + G * k < L) {
                     sum += v[k]; lo = fmin(lo, v[k]); hi = fmax(hi, v[k]);
-                    r2[k] = fma(v[k], v[k], r2[k]);
+                    r2[k * 128] = a == 0 ? v[k] * v[k] : fma(v[k], v[k], r2[k * 128]);
                 }
             }
 #pragma unroll
@@ -69,11 +68,13 @@ k_window_features_v3(const double* __restrict__ x, const double* __restrict__ y,
                     ab += fabs(d);
                     const int bq = __double2int_rd((c - lo) * scale);
                     atomicAdd(&bins_w[bq >= 9 ? 9 : bq], 1u);
-                    if (i >= 1 && i + 1 < L) {
-                        const bool is_pk = c > __ldg(p + i - 1) && c >= __ldg(p + i + 1);
-                        pk |= (is_pk ? 1u : 0u) << k;
-                        pm = fmax(pm, is_pk ? c : -INFINITY);
-                    }
+                    // local maximum test without branches: both neighbours are always loaded (clamped at the
+                    // window edges, where the result is masked off)
+                    const bool interior = i >= 1 && i + 1 < L;
+                    const double lft = __ldg(p + (i >= 1 ? i - 1 : i)), rgt = __ldg(p + (i + 1 < L ? i + 1 : i));
+                    const bool is_pk = interior & (c > lft) & (c >= rgt);
+                    pk |= (is_pk ? 1u : 0u) << k;
+                    pm = is_pk ? fmax(pm, c) : pm;
                 }
             }
             int npk = __popc(pk);
@@ -97,7 +98,7 @@ k_window_features_v3(const double* __restrict__ x, const double* __restrict__ y,
                     const double t = __dsub_rn(pm, __dmul_rn(__dmul_rn((double)(kk + 1), 0.1), R));
                     int c3 = 0;
 #pragma unroll
-                    for (int k = 0; k < KITER; k++) c3 += (((pk >> k) & 1u) && v[k] >= t) ? 1 : 0;
+                    for (int k = 0; k < KITER; k++) c3 += (((pk >> k) & 1u) & (v[k] >= t)) ? 1 : 0;
 #pragma unroll
                     for (int m = 4; m >= 1; m >>= 1) c3 += __shfl_xor_sync(gmask, c3, m);
                     if (c3 >= 3) { tau = t; break; }
@@ -106,7 +107,11 @@ k_window_features_v3(const double* __restrict__ x, const double* __restrict__ y,
             int first = 0x7fffffff, last = -1, cnt = 0;
 #pragma unroll
             for (int k = 0; k < KITER; k++)
-                if (((pk >> k) & 1u) && v[k] >= tau) { const int i = sub + G * k; first = min(first, i); last = max(last, i); cnt++; }
+            {
+                const bool sel = ((pk >> k) & 1u) & (v[k] >= tau);
+                const int i = sub + G * k;
+                first = sel ? min(first, i) : first; last = sel ? max(last, i) : last; cnt += sel ? 1 : 0;
+            }
 #pragma unroll
             for (int m = 4; m >= 1; m >>= 1) {
                 first = min(first, __shfl_xor_sync(0xffffffffu, first, m));
@@ -141,7 +146,7 @@ k_window_features_v3(const double* __restrict__ x, const double* __restrict__ y,
 #pragma unroll
         for (int k = 0; k < KITER; k++) {
             if (EXACT || sub + G * k < L) {
-                const double s2 = r2[k];
+                const double s2 = r2[k * 128];
                 const double r = (double)rsqrtf((float)s2);
                 double yv = s2 * r;
                 yv = fma(0.5 * r, fma(-yv, yv, s2), yv);

@@ -65,19 +65,21 @@ class WisdmWindowFeaturizer(Transformer):
             c[dataset._resolve(self.getUserCol())], c[dataset._resolve(self.getActivityCol())],
             c[dataset._resolve(self.getTimestampCol())], c[dataset._resolve(self.getXCol())],
             c[dataset._resolve(self.getYCol())], c[dataset._resolve(self.getZCol())])
-        f = core.to_host(feats)
-        nw = f.shape[0]
+        nw = feats.shape[0]
+        # scalar columns: transpose on the device so every host column is one contiguous row of the copy
+        fT = core.to_host(feats.t().contiguous())
         cols, types = {}, {}
         cols["UID"], types["UID"] = np.arange(1, nw + 1, dtype=np.int32), "int"
         cols["USER"], types["USER"] = core.to_host(wu), "int"
         for j, name in enumerate(core.WINDOW_FEATURE_NAMES):
-            cols[name], types[name] = np.ascontiguousarray(f[:, j]), "double"
+            cols[name], types[name] = fT[j], "double"
         cols["ACTIVITY"], types["ACTIVITY"] = core.to_host(wa), "int"
         meta = {}
         if self.isDefined(self.outputCol):
-            fv = np.where(np.isnan(f), self.getUnknownPeakValue(), f)
-            cols[self.getOutputCol()], types[self.getOutputCol()] = VectorColumn(f.shape[1], dense=fv), "vector"
-            meta[self.getOutputCol()] = {"ml_attr": {"num_attrs": f.shape[1], "arity": np.zeros(f.shape[1], np.int32)}}
+            # the assembled vector column stays in HBM for the estimator that consumes it; its host copy is lazy
+            fv = torch.nan_to_num(feats, nan=self.getUnknownPeakValue())
+            cols[self.getOutputCol()], types[self.getOutputCol()] = VectorColumn(feats.shape[1], device=fv), "vector"
+            meta[self.getOutputCol()] = {"ml_attr": {"num_attrs": feats.shape[1], "arity": np.zeros(feats.shape[1], np.int32)}}
         if self.isDefined(self.labelCol):
             cols[self.getLabelCol()], types[self.getLabelCol()] = cols["ACTIVITY"].astype(np.float64), "double"
         return DataFrame(cols, types, meta)

@@ -79,7 +79,11 @@ def _device_features(col):
     from har_b200 import core
     if col.is_sparse:
         return core.csr_to_dense(col.indptr, col.indices, col.values, len(col), col.size)
-    return core.dev(col.dense, np.float64)
+    dev = getattr(col, "_dev", None)
+    if dev is not None and dev.is_cuda:
+        return dev                                   # still resident from the stage that produced it
+    col._dev = core.dev(col.dense, np.float64)       # keep it for the next fit / transform on this column
+    return col._dev
 
 
 class _TreeEstimatorBase(Estimator, _TreeClassifierParams):

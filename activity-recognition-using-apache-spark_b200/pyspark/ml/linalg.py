@@ -175,22 +175,37 @@ class VectorColumn:
     row-major ``f64[n, size]`` matrix.  These buffers are what is handed to the CUDA library.
     """
 
-    def __init__(self, size, indptr=None, indices=None, values=None, dense=None):
+    def __init__(self, size, indptr=None, indices=None, values=None, dense=None, device=None):
+        """`device`: an optional CUDA tensor [n, size] holding the same dense values; the host copy is then
+        materialised only when something on the host reads it (keeps the column resident in HBM between the
+        stages that produce and consume it)."""
         self.size = int(size)
-        self.dense = None if dense is None else np.ascontiguousarray(dense, dtype=np.float64)
-        if dense is None:
+        self._dev = device
+        self._dense = None if dense is None else np.ascontiguousarray(dense, dtype=np.float64)
+        if dense is None and device is None:
             self.indptr = np.asarray(indptr, dtype=np.int64)
             self.indices = np.asarray(indices, dtype=np.int32)
             self.values = np.asarray(values, dtype=np.float64)
+            self._sparse = True
         else:
             self.indptr = self.indices = self.values = None
+            self._sparse = False
+
+    @property
+    def dense(self):
+        if self._dense is None and self._dev is not None:
+            from har_b200 import core
+            self._dense = core.to_host(self._dev)
+        return self._dense
 
     @property
     def is_sparse(self):
-        return self.dense is None
+        return self._sparse
 
     def __len__(self):
-        return len(self.indptr) - 1 if self.is_sparse else self.dense.shape[0]
+        if self.is_sparse:
+            return len(self.indptr) - 1
+        return int(self._dev.shape[0]) if self._dense is None else self._dense.shape[0]
 
     def row(self, i):
         if self.is_sparse:

@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--trees", type=int, default=100)
     ap.add_argument("--depth", type=int, default=10)
     ap.add_argument("--partitions", type=int, default=1024, help="Spark partitions per GPU shard (bagging streams)")
-    ap.add_argument("--cpu-sample", type=int, default=10_000_000, help="stream samples of the bounded CPU baseline")
+    ap.add_argument("--cpu-sample", type=int, default=30_000_000, help="stream samples of the bounded CPU baseline")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -113,40 +113,70 @@ def workload_config(args, world):
 
 
 class ClockSampler:
-    """nvidia-smi sampled during the timed region (B200_PROFILING.md clocks line)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock / throttle reasons sampled DURING the timed region (B200_PROFILING.md clocks line).  Uses NVML
+    in-process (cheap queries from a thread; a looping `nvidia-smi -lms` process was seen to stall CUDA API calls
+    for tens of ms); falls back to one-shot nvidia-smi calls if pynvml is missing."""
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
 
-    def __init__(self, gpu_index):
-        self.idx, self.rows, self.proc = gpu_index, [], None
+    def __init__(self, gpu_index, period_s=0.1):
+        self.idx, self.period, self.rows, self._stop, self._thr = gpu_index, period_s, [], threading.Event(), None
+        self._nvml = None
+
+    def _physical_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [v for v in vis.split(",") if v.strip() != ""]
+            if self.idx < len(ids) and ids[self.idx].strip().isdigit():
+                return int(ids[self.idx])
+        return self.idx
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200",
-                                          "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index())
         except Exception:
-            self.proc = None
+            self._nvml = None
+        self._thr = threading.Thread(target=self._run, daemon=True)
+        self._thr.start()
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+    def _sample(self):
+        if self._nvml is not None:
+            n = self._nvml
+            sm = n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM)
+            mx = n.nvmlDeviceGetMaxClockInfo(self._h, n.NVML_CLOCK_SM)
+            try:
+                mask = n.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+            except Exception:
+                mask = n.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+            self.rows.append((float(sm), float(mx), int(mask)))
+        else:
+            q = "clocks.sm,clocks.max.sm,clocks_event_reasons.active"
+            out = subprocess.run(["nvidia-smi", "--query-gpu=" + q, "--format=csv,noheader,nounits", "-i", str(self._physical_index())],
+                                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=10).stdout.strip().split(",")
+            self.rows.append((float(out[0]), float(out[1]), int(out[2].strip(), 16)))
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self._sample()
+            except Exception:
+                pass
+            self._stop.wait(self.period if self._nvml is not None else 1.0)
 
     def stop(self):
-        if self.proc:
-            self.proc.terminate()
-        sm, mx, reasons = [], 0.0, set()
-        for r in self.rows:
-            try:
-                sm.append(float(r[1])); mx = max(mx, float(r[2]))
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
-            except (ValueError, IndexError):
-                pass
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        self._stop.set()
+        if self._thr:
+            self._thr.join(timeout=5)
+        sm = sorted(r[0] for r in self.rows)
+        reasons = set()
+        for _, _, mask in self.rows:
+            for name, bit in self.REASONS:
+                if mask & bit:
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max((r[1] for r in self.rows), default=None),
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self._nvml is not None else "nvidia-smi"}
 
 
 def measured_peaks():
@@ -229,9 +259,12 @@ def run_ours(args):
     rec = []
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     e0.record()
-    for _ in range(args.steps):
+    marks[0].record()
+    for i in range(args.steps):
         device_step(rec)
+        marks[i + 1].record()
     e1.record()
     barrier()
     launches = core.launch_count()
@@ -352,6 +385,7 @@ def run_ours(args):
                        "node_groups": rec[-1][3], "device_batches": rec[-1][4], "allreduce_calls": rec[-1][5][0],
                        "allreduce_bytes": rec[-1][5][1], "train_accuracy": train_acc},
             "roofline": roofline, "window_stage_roofline": window_roof, "kernels": roofs,
+            "step_ms": [marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps)],
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk}
     print(json.dumps(line))
     if world > 1:
