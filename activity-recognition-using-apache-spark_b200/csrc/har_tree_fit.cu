@@ -787,6 +787,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             bool leaf = false;
             emit_node(pf, trees[t], tree_stats[t], 0, 0, &leaf);
         });
+        if (trace) fprintf(stderr, "[har_forest_fit]   toNode: parallel emit %.2f ms\n", ms_since(t_emit));
         size_t total_nodes = 0;
         for (int t = 0; t < T; t++) { fo->tree_off[t] = (int64_t)total_nodes; total_nodes += parts[t].feature.size(); }
         fo->feature.reserve(total_nodes); fo->left.reserve(total_nodes); fo->right.reserve(total_nodes);

@@ -96,22 +96,24 @@ k_window_features_v3(const double* __restrict__ x, const double* __restrict__ y,
 #pragma unroll 1
                 for (int kk = 0; kk < 9; kk++) {
                     const double t = __dsub_rn(pm, __dmul_rn(__dmul_rn((double)(kk + 1), 0.1), R));
-                    int c3 = 0;
+                    unsigned mt = 0;
 #pragma unroll
-                    for (int k = 0; k < KITER; k++) c3 += (((pk >> k) & 1u) & (v[k] >= t)) ? 1 : 0;
+                    for (int k = 0; k < KITER; k++) mt |= (v[k] >= t ? 1u : 0u) << k;
+                    int c3 = __popc(mt & pk);
 #pragma unroll
                     for (int m = 4; m >= 1; m >>= 1) c3 += __shfl_xor_sync(gmask, c3, m);
                     if (c3 >= 3) { tau = t; break; }
                 }
             }
-            int first = 0x7fffffff, last = -1, cnt = 0;
+            // admitted peaks of this lane as a bit mask over k; i = sub + 8k is monotone in k, so the lane's
+            // first / last admitted index and their count come from ffs / clz / popc
+            unsigned adm = 0;
 #pragma unroll
-            for (int k = 0; k < KITER; k++)
-            {
-                const bool sel = ((pk >> k) & 1u) & (v[k] >= tau);
-                const int i = sub + G * k;
-                first = sel ? min(first, i) : first; last = sel ? max(last, i) : last; cnt += sel ? 1 : 0;
-            }
+            for (int k = 0; k < KITER; k++) adm |= (v[k] >= tau ? 1u : 0u) << k;
+            adm &= pk;
+            int first = adm ? sub + G * (__ffs(adm) - 1) : 0x7fffffff;
+            int last = adm ? sub + G * (31 - __clz(adm)) : -1;
+            int cnt = __popc(adm);
 #pragma unroll
             for (int m = 4; m >= 1; m >>= 1) {
                 first = min(first, __shfl_xor_sync(0xffffffffu, first, m));

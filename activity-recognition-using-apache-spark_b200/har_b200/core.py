@@ -219,16 +219,26 @@ class Forest:
         T, Cn, F, tot = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int64()
         N.check(N.lib().har_forest_shape(self._h, C.byref(T), C.byref(Cn), C.byref(F), C.byref(tot)))
         self.T, self.C, self.F, self.total_nodes = T.value, Cn.value, F.value, tot.value
-        n = self.total_nodes
-        self.tree_off = np.zeros(self.T + 1, np.int64)
-        self.feature = np.zeros(n, np.int32); self.left = np.zeros(n, np.int32); self.right = np.zeros(n, np.int32)
-        self.node_id = np.zeros(n, np.int32); self.arity = np.zeros(n, np.int32)
-        self.threshold = np.zeros(n, np.float64); self.left_mask = np.zeros(n, np.uint64)
-        self.prediction = np.zeros(n, np.float64); self.impurity = np.zeros(n, np.float64)
-        self.gain = np.zeros(n, np.float64); self.stats = np.zeros((n, self.C), np.float64)
-        N.check(N.lib().har_forest_export(self._h, *[hptr(getattr(self, k)) for k in self.FIELDS]))
+        self._arrays = None          # flat node arrays are copied out of the handle on first use
         self.thresholds = self.nsplits = None
         self.num_groups = self.num_batches = self.num_launches = 0
+
+    def _export(self):
+        n = self.total_nodes
+        a = {"tree_off": np.zeros(self.T + 1, np.int64), "feature": np.zeros(n, np.int32), "left": np.zeros(n, np.int32),
+             "right": np.zeros(n, np.int32), "node_id": np.zeros(n, np.int32), "arity": np.zeros(n, np.int32),
+             "threshold": np.zeros(n, np.float64), "left_mask": np.zeros(n, np.uint64), "prediction": np.zeros(n, np.float64),
+             "impurity": np.zeros(n, np.float64), "gain": np.zeros(n, np.float64), "stats": np.zeros((n, self.C), np.float64)}
+        N.check(N.lib().har_forest_export(self._h, *[hptr(a[k]) for k in self.FIELDS]))
+        self._arrays = a
+
+    def __getattr__(self, name):
+        # only reached for attributes not set in __init__: the lazily exported node arrays
+        if name in Forest.FIELDS:
+            if self.__dict__.get("_arrays") is None:
+                self._export()
+            return self.__dict__["_arrays"][name]
+        raise AttributeError(name)
 
     @classmethod
     def from_arrays(cls, T, Cn, F, tree_off, feature, left, right, arity, threshold, left_mask, stats):
