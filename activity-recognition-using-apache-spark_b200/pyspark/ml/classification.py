@@ -3,7 +3,7 @@
 har_b200 (include/har_b200.h: har_forest_fit / har_forest_predict).
 
 Reference call sites: Main/main.py:297-305 (DT), :478-486 (RF), and via CrossValidator :389-400, :570-581.
-LogisticRegression (main.py:115) is outside the hot path and not provided.
+LogisticRegression (main.py:115) is outside the hot path: `_host_lr.py` is a host-only stand-in so main.py completes.
 """
 import numpy as np
 
@@ -11,8 +11,11 @@ from . import Estimator, Model
 from .linalg import DenseVector, VectorColumn
 from .param import Param, Params, TypeConverters, _make_accessors
 
+from ._host_lr import LogisticRegression, LogisticRegressionModel  # host-only filler, outside the hot path
+
 __all__ = ["DecisionTreeClassifier", "DecisionTreeClassificationModel",
-           "RandomForestClassifier", "RandomForestClassificationModel"]
+           "RandomForestClassifier", "RandomForestClassificationModel",
+           "LogisticRegression", "LogisticRegressionModel"]
 
 
 class _TreeClassifierParams(Params):

@@ -206,8 +206,9 @@ def _fmt_cell(v, t):
 
 
 class GroupedData:
-    def __init__(self, df, names):
+    def __init__(self, df, names, typed=None):
         self._df, self._names = df, names
+        self._typed = typed or names           # Spark keeps the spelling the caller used (result.txt:34 "activity")
 
     def count(self):
         df = self._df
@@ -216,10 +217,10 @@ class GroupedData:
         for k in keys:
             counts[k] = counts.get(k, 0) + 1
         cols, types = OrderedDict(), OrderedDict()
-        for j, n in enumerate(self._names):
+        for j, (n, shown) in enumerate(zip(self._names, self._typed)):
             vals = [k[j] for k in counts]
-            cols[n] = np.array(vals, dtype=df._cols[n].dtype)
-            types[n] = df._types[n]
+            cols[shown] = np.array(vals, dtype=df._cols[n].dtype)
+            types[shown] = df._types[n]
         cols["count"] = np.array(list(counts.values()), dtype=np.int64)
         types["count"] = "bigint"
         return DataFrame(cols, types)
@@ -423,7 +424,8 @@ class DataFrame:
         return "".join(out)
 
     def groupBy(self, *names):
-        return GroupedData(self, [self._resolve(n._name if isinstance(n, Column) else n) for n in names])
+        typed = [n._name if isinstance(n, Column) else n for n in names]
+        return GroupedData(self, [self._resolve(n) for n in typed], typed)
 
     groupby = groupBy
 
@@ -475,9 +477,18 @@ class DataFrame:
             else:
                 a = c.astype(np.float64)
                 cnt = len(a)
-                mean = a.sum() / cnt if cnt else float("nan")
-                # Spark: sample standard deviation (n-1)
-                sd = float(np.sqrt(((a - mean) ** 2).sum() / (cnt - 1))) if cnt > 1 else float("nan")
+                # Spark's aggregates, row by row in one partition: Average = running sum / count;
+                # StddevSamp = CentralMomentAgg's online update (n, avg, m2), sqrt(m2 / (n - 1))
+                total, avg, m2, k = 0.0, 0.0, 0.0, 0.0
+                for x in a.tolist():
+                    total += x
+                    k += 1.0
+                    delta = x - avg
+                    delta_n = delta / k
+                    avg += delta_n
+                    m2 += delta * (delta - delta_n)
+                mean = total / cnt if cnt else float("nan")
+                sd = float(np.sqrt(m2 / (cnt - 1))) if cnt > 1 else float("nan")
                 mn, mx = (c.min(), c.max()) if cnt else (None, None)
                 fm = (lambda v: str(int(v))) if t in ("int", "bigint") else (lambda v: java_double_str(v))
                 out = [str(cnt), java_double_str(mean), java_double_str(sd), fm(mn), fm(mx)]

@@ -15,7 +15,7 @@ def test_csv_schema_matches_spark_inference(wisdm, golden):
 def test_activity_counts_and_label_order(wisdm, golden):
     from pyspark.sql.functions import col
     out = wisdm["data"].groupBy("activity").count().orderBy(col("count").desc())
-    got = [[str(a), str(c)] for a, c in zip(out._cols["ACTIVITY"], out._cols["count"])]
+    got = [[str(a), str(c)] for a, c in zip(out._cols["activity"], out._cols["count"])]
     want = [[c.strip() for c in row] for row in gv(golden, "activity_counts")]
     assert got == want                                                       # result.txt:36-41
     labels = [s for s in wisdm["pipeline"].stages if getattr(s, "getOutputCol", lambda: "")() == "label"][0].labels
