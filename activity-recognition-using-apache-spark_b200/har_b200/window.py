@@ -11,7 +11,7 @@ import torch
 from pyspark.ml import Transformer
 from pyspark.ml.linalg import VectorColumn
 from pyspark.ml.param import Param, Params, TypeConverters, _make_accessors
-from pyspark.sql import DataFrame
+from pyspark.sql import DataFrame, DeviceColumn
 
 from . import core
 
@@ -66,14 +66,15 @@ class WisdmWindowFeaturizer(Transformer):
             c[dataset._resolve(self.getTimestampCol())], c[dataset._resolve(self.getXCol())],
             c[dataset._resolve(self.getYCol())], c[dataset._resolve(self.getZCol())])
         nw = feats.shape[0]
-        # scalar columns: transpose on the device so every host column is one contiguous row of the copy
-        fT = core.to_host(feats.t().contiguous())
+        # the 46 scalar columns of the reference schema stay in HBM (DeviceColumn) until something on the host
+        # reads them; transposed once on the device so each column is one contiguous row
+        fT = feats.t().contiguous()
         cols, types = {}, {}
         cols["UID"], types["UID"] = np.arange(1, nw + 1, dtype=np.int32), "int"
-        cols["USER"], types["USER"] = core.to_host(wu), "int"
+        cols["USER"], types["USER"] = DeviceColumn(wu, np.int32), "int"
         for j, name in enumerate(core.WINDOW_FEATURE_NAMES):
-            cols[name], types[name] = fT[j], "double"
-        cols["ACTIVITY"], types["ACTIVITY"] = core.to_host(wa), "int"
+            cols[name], types[name] = DeviceColumn(fT[j], np.float64), "double"
+        cols["ACTIVITY"], types["ACTIVITY"] = DeviceColumn(wa, np.int32), "int"
         meta = {}
         if self.isDefined(self.outputCol):
             # the assembled vector column stays in HBM for the estimator that consumes it; its host copy is lazy
@@ -81,7 +82,7 @@ class WisdmWindowFeaturizer(Transformer):
             cols[self.getOutputCol()], types[self.getOutputCol()] = VectorColumn(feats.shape[1], device=fv), "vector"
             meta[self.getOutputCol()] = {"ml_attr": {"num_attrs": feats.shape[1], "arity": np.zeros(feats.shape[1], np.int32)}}
         if self.isDefined(self.labelCol):
-            cols[self.getLabelCol()], types[self.getLabelCol()] = cols["ACTIVITY"].astype(np.float64), "double"
+            cols[self.getLabelCol()], types[self.getLabelCol()] = DeviceColumn(wa.to(torch.float64), np.float64), "double"
         return DataFrame(cols, types, meta)
 
 

@@ -7,7 +7,13 @@ LogisticRegression (main.py:115) is outside the hot path: `_host_lr.py` is a hos
 """
 import numpy as np
 
+try:
+    import torch
+except ImportError:  # pragma: no cover
+    torch = None
+
 from . import Estimator, Model
+from ..sql import DeviceColumn
 from .linalg import DenseVector, VectorColumn
 from .param import Param, Params, TypeConverters, _make_accessors
 
@@ -68,7 +74,7 @@ def _num_classes(dataset, label_name, y):
         return 2
     if len(y) == 0:
         raise ValueError("ML algorithm was given empty dataset.")
-    mx = float(np.max(y))
+    mx = float(y.max())
     if mx != int(mx) or mx < 0:
         raise ValueError("Classifier found max label value = %s but requires integers in range [0, ... %d)" % (mx, 2**31 - 1))
     if int(mx) + 1 > 100:
@@ -99,7 +105,11 @@ class _TreeEstimatorBase(Estimator, _TreeClassifierParams):
         if dataset._types[fname] != "vector":
             raise TypeError("Column %s must be of type vector but was actually %s." % (fname, dataset._types[fname]))
         col = dataset._cols[fname]
-        y = np.asarray(dataset._cols[lname], dtype=np.float64)
+        yraw = dataset._cols.raw(lname)
+        if isinstance(yraw, DeviceColumn) and yraw.tensor.is_cuda:
+            y = yraw.tensor.to(torch.float64)            # label column still resident in HBM
+        else:
+            y = np.asarray(dataset._cols[lname], dtype=np.float64)
         C = _num_classes(dataset, lname, y)
         arity = dataset._meta.get(fname, {}).get("ml_attr", {}).get("arity")
         imp = self.getOrDefault(self.impurity).lower()
@@ -159,9 +169,21 @@ class _TreeModelBase(Model, _TreeClassifierParams):
         col = dataset._cols[fname]
         X = _device_features(col)
         from har_b200 import core
+        from ..sql import DeviceColumn
         raw, prob, pred = forest.predict(X, is_forest=is_forest)
+        use_thresholds = self.isDefined(self.thresholds) and self.getOrDefault(self.thresholds) is not None
+        if not use_thresholds and getattr(raw, "is_cuda", False):
+            # output columns stay in HBM until read (rawPrediction / probability as device-backed vector columns)
+            df = dataset
+            if self.getRawPredictionCol():
+                df = df.withColumn(self.getRawPredictionCol(), VectorColumn(forest.C, device=raw), "vector")
+            if self.getProbabilityCol():
+                df = df.withColumn(self.getProbabilityCol(), VectorColumn(forest.C, device=prob), "vector")
+            if self.getPredictionCol():
+                df = df.withColumn(self.getPredictionCol(), DeviceColumn(pred, np.float64), "double")
+            return df
         raw, prob, pred = core.to_host(raw), core.to_host(prob), core.to_host(pred)
-        if self.isDefined(self.thresholds) and self.getOrDefault(self.thresholds) is not None:
+        if use_thresholds:
             th = np.asarray(self.getOrDefault(self.thresholds), dtype=np.float64)
             if len(th) != forest.C:
                 raise ValueError("thresholds must have length equal to numClasses (%d)" % forest.C)

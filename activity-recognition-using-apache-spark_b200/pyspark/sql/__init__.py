@@ -20,7 +20,7 @@ from ..ml.linalg import VectorColumn, java_double_str
 from .._rng import XORShiftRandom
 from .column import Column, col, _ColRef
 
-__all__ = ["SQLContext", "SparkSession", "DataFrame", "Row", "Column"]
+__all__ = ["SQLContext", "SparkSession", "DataFrame", "Row", "Column", "DeviceColumn"]
 
 _SPARK_TYPE_NAMES = {"int": "integer", "bigint": "long", "double": "double", "string": "string",
                      "vector": "vector", "boolean": "boolean"}
@@ -195,6 +195,50 @@ def createDataFrame(data, schema=None):
     return DataFrame(cols, types)
 
 
+class DeviceColumn:
+    """A scalar column whose values still live in HBM (a 1-d CUDA tensor); it is copied to the host the
+    first time anything on the host reads it — the facade's counterpart of Spark's lazy transformations."""
+
+    def __init__(self, tensor, dtype):
+        self.tensor, self.dtype = tensor, np.dtype(dtype)
+
+    def __len__(self):
+        return int(self.tensor.shape[0])
+
+    def materialize(self):
+        from har_b200 import core
+        return np.ascontiguousarray(core.to_host(self.tensor.contiguous()), dtype=self.dtype)
+
+
+class _Cols(OrderedDict):
+    """Column store: name -> numpy array / VectorColumn, with DeviceColumn entries materialised on first read."""
+
+    def __init__(self, other=()):
+        OrderedDict.__init__(self)
+        items = dict.items(other) if isinstance(other, dict) else other      # raw entries: nothing is materialised
+        for k, v in items:
+            OrderedDict.__setitem__(self, k, v)
+
+    def raw(self, k):
+        return OrderedDict.__getitem__(self, k)
+
+    def __getitem__(self, k):
+        v = OrderedDict.__getitem__(self, k)
+        if isinstance(v, DeviceColumn):
+            v = v.materialize()
+            OrderedDict.__setitem__(self, k, v)
+        return v
+
+    def get(self, k, default=None):
+        return self[k] if k in self else default
+
+    def values(self):
+        return [self[k] for k in self.keys()]
+
+    def items(self):
+        return [(k, self[k]) for k in self.keys()]
+
+
 def _fmt_cell(v, t):
     if v is None:
         return "null"
@@ -228,10 +272,10 @@ class GroupedData:
 
 class DataFrame:
     def __init__(self, cols, types, meta=None, partitions=None):
-        self._cols = OrderedDict(cols)
+        self._cols = _Cols(cols)
         self._types = OrderedDict(types)
         self._meta = dict(meta or {})
-        n = len(next(iter(self._cols.values()))) if self._cols else 0
+        n = len(self._cols.raw(next(iter(self._cols.keys())))) if self._cols else 0
         # row offsets of the Spark partitions this frame stands for (one by default: the
         # reference's 1.2 MB CSV is a single input partition)
         self._partitions = list(partitions) if partitions is not None else [0, n]
@@ -293,7 +337,7 @@ class DataFrame:
             if isinstance(n, Column):
                 n = n._name
             r = self._resolve(n)
-            cols[r], types[r] = self._cols[r], self._types[r]
+            cols[r], types[r] = self._cols.raw(r), self._types[r]
             if r in self._meta:
                 meta[r] = self._meta[r]
         return DataFrame(cols, types, meta, self._partitions)
@@ -304,12 +348,14 @@ class DataFrame:
 
     def withColumn(self, name, data, dtype=None, metadata=None):
         """Facade extension: attach a materialised column (numpy array / VectorColumn)."""
-        cols, types, meta = OrderedDict(self._cols), OrderedDict(self._types), dict(self._meta)
+        cols, types, meta = _Cols(self._cols), OrderedDict(self._types), dict(self._meta)
         if isinstance(data, Column):
             data = data._eval(self)
         if dtype is None:
             if isinstance(data, VectorColumn):
                 dtype = "vector"
+            elif isinstance(data, DeviceColumn):
+                dtype = {"f": "double", "i": "bigint"}.get(data.dtype.kind, "double")
             else:
                 data = np.asarray(data)
                 dtype = {"f": "double", "i": "bigint", "u": "bigint", "b": "boolean"}.get(data.dtype.kind, "string")
