@@ -120,3 +120,53 @@ HAR_API int har_debug_profile_read(int id, double* ms, long long* launches, doub
     if (units) *units = har::g_acc[id].units;
     return HAR_OK;
 }
+
+// ---- shared-memory atomic micro-benchmark (the roofline denominator of k_node_hist) ------------------
+// mode 0: every lane of a warp hits its own bank (conflict-free upper bound);
+// mode 1: uniformly random counters inside a `words`-sized tile (what a histogram with well-spread bins does).
+namespace {
+__global__ void __launch_bounds__(256)
+k_smem_atomic_peak(int mode, int words, int iters, unsigned* sink) {
+    extern __shared__ unsigned sh_ctr[];
+    for (int i = threadIdx.x; i < words; i += blockDim.x) sh_ctr[i] = 0;
+    __syncthreads();
+    unsigned s = (blockIdx.x * 256u + threadIdx.x) * 2654435761u + 12345u;
+    const int lane = threadIdx.x & 31;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            s = s * 1664525u + 1013904223u;
+            // words is a power of two here: masks instead of modulo keep the loop at ~4 instructions per atomic
+            unsigned idx = mode == 0 ? ((((s >> 8) & (unsigned)(words / 32 - 1)) << 5) + lane) : ((s >> 8) & (unsigned)(words - 1));
+            atomicAdd(&sh_ctr[idx], 1u);
+        }
+    }
+    __syncthreads();
+    unsigned acc = 0;
+    for (int i = threadIdx.x; i < words; i += blockDim.x) acc += sh_ctr[i];
+    if (acc == 0xffffffffu) sink[0] = acc;
+}
+}  // namespace
+
+// Returns shared-memory atomics per second (device-wide) measured with CUDA events; words = power of two <= 8192.
+HAR_API int har_debug_smem_atomic_peak(int mode, int words, double* atomics_per_s, har_stream_t stream) {
+    if (words < 32 || words > 8192 || (words & (words - 1)) || !atomics_per_s)
+        return har::fail(HAR_E_INVALID, "har_debug_smem_atomic_peak: words must be a power of two in [32, 8192]");
+    cudaStream_t s = (cudaStream_t)stream;
+    har::DevBuf<unsigned> sink;
+    HAR_CUDA(sink.alloc(1, s));
+    const int iters = 2000, blocks = har::kNumSMs * 4 * 4;
+    cudaEvent_t a, b;
+    HAR_CUDA(cudaEventCreate(&a)); HAR_CUDA(cudaEventCreate(&b));
+    HAR_CUDA(cudaFuncSetAttribute(k_smem_atomic_peak, cudaFuncAttributeMaxDynamicSharedMemorySize, 12288 * 4));
+    k_smem_atomic_peak<<<blocks, 256, words * 4, s>>>(mode, words, 50, sink.p);      // warm-up
+    HAR_CUDA(cudaEventRecord(a, s));
+    k_smem_atomic_peak<<<blocks, 256, words * 4, s>>>(mode, words, iters, sink.p);
+    HAR_CUDA(cudaEventRecord(b, s));
+    HAR_CUDA(cudaEventSynchronize(b));
+    float ms = 0;
+    HAR_CUDA(cudaEventElapsedTime(&ms, a, b));
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    *atomics_per_s = (double)blocks * 256.0 * iters * 16.0 / (ms * 1e-3);
+    return HAR_OK;
+}

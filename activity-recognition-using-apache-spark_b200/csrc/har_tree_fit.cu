@@ -409,7 +409,7 @@ HAR_API int har_node_histogram(const uint8_t* d_bins, int64_t ldb, const uint8_t
     HAR_CUDA(cudaMemcpyAsync(d_io.p, item_off, sizeof item_off, cudaMemcpyHostToDevice, s));
     HAR_CUDA(cudaMemcpyAsync(d_loff.p, loff.data(), sizeof(int32_t) * (F + 1), cudaMemcpyHostToDevice, s));
     HAR_CUDA(cudaMemsetAsync(d_kind.p, KIND_CONT, F, s));
-    const size_t smem = (HIST_TILE_WORDS + 32 + HIST_FTAB) * sizeof(uint32_t);
+    const size_t smem = (HIST_TILE_WORDS + 32 + HIST_FTAB + HIST_FTAB / 16) * sizeof(uint32_t);
     const bool vec = (ldb % 16 == 0) && ((reinterpret_cast<uintptr_t>(d_bins) & 15) == 0);
     if (vec) {
         HAR_CUDA(cudaFuncSetAttribute(k_node_hist<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -566,7 +566,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_CUDA(d_loff_all.alloc(F + 1, s));
         HAR_CUDA(cudaMemcpyAsync(d_loff_all.p, m.loff.data(), sizeof(int32_t) * (F + 1), cudaMemcpyHostToDevice, s));
     }
-    const size_t hist_smem = (HIST_TILE_WORDS + 32 + HIST_FTAB) * sizeof(uint32_t);
+    const size_t hist_smem = (HIST_TILE_WORDS + 32 + HIST_FTAB + HIST_FTAB / 16) * sizeof(uint32_t);
     HAR_CUDA(cudaFuncSetAttribute(k_node_hist<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem));
     HAR_CUDA(cudaFuncSetAttribute(k_node_hist<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem));
     const size_t bs_smem = ((size_t)BS_ROWS * (C + 1) + 64 * C) * 4 * (BS_THREADS / 32) + MAX_CAT * (BS_THREADS / 32) * 12 + 128 +

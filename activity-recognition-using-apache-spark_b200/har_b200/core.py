@@ -82,6 +82,14 @@ def launch_count(reset=False):
     return int(N.lib().har_debug_launch_count(1 if reset else 0))
 
 
+def smem_atomic_peak(mode, words=8192):
+    """Measured shared-memory atomic throughput (atomics/s, whole device): mode 0 conflict-free, 1 random."""
+    require_cuda()
+    v = C.c_double()
+    N.check(N.lib().har_debug_smem_atomic_peak(mode, words, C.byref(v), stream()))
+    return v.value
+
+
 PROFILE_IDS = ("node_hist", "best_split", "part_count", "part_scatter", "window_features", "seg_tiles", "predict",
                "bin_features", "find_splits", "bag_weights")
 

@@ -380,6 +380,13 @@ def run_ours(args):
         k = kern["node_hist"]
         roofline["limiter"] = "shared-memory atomics (red.shared.add.u32), not HBM"
         roofline["smem_atomics_per_s"] = k["units_per_step"] * F / (k["ms_per_step"] * 1e-3)
+        try:       # measured micro-benchmark peaks of red.shared.add.u32 on this GPU (same tile size as the kernel)
+            pk_free, pk_rand = core.smem_atomic_peak(0), core.smem_atomic_peak(1)
+            roofline["smem_atomic_peak_conflict_free_per_s"] = pk_free
+            roofline["smem_atomic_peak_random_per_s"] = pk_rand
+            roofline["smem_atomic_frac_of_random_peak"] = roofline["smem_atomics_per_s"] / pk_rand
+        except Exception as e:
+            roofline["smem_atomic_peak_error"] = repr(e)
     win_ms = stage["window_ms"]
     window_roof = {"bound": "hbm", "achieved": BYTES_PER_SAMPLE * n / (win_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                    "bytes_per_sample": BYTES_PER_SAMPLE, "stage_ms": win_ms}
