@@ -5,7 +5,9 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/har_b200.h"
@@ -77,6 +79,21 @@ struct DevBuf {
 };
 
 inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// Small fork-join helper for the host-side (driver) work; `go` = false runs inline.
+template <typename Fn>
+void parallel_for(int n, bool go, Fn fn) {
+    unsigned hw = std::thread::hardware_concurrency();
+    int nt = (int)std::min<unsigned>(hw ? hw : 1, 8);
+    if (!go || nt <= 1 || n < 2) { for (int i = 0; i < n; i++) fn(i); return; }
+    nt = std::min(nt, n);
+    std::vector<std::thread> th;
+    th.reserve(nt);
+    for (int k = 0; k < nt; k++) th.emplace_back([=, &fn] { for (int i = k; i < n; i += nt) fn(i); });
+    for (auto& t : th) t.join();
+}
+
+
 
 // java.lang.Double.compare total order as a sortable unsigned key (NaN canonical, greatest).
 __host__ __device__ inline uint64_t jd_key(double x) {

@@ -101,25 +101,33 @@ int build_device_tables(har_forest* f, int is_forest, cudaStream_t s) {
     const int T = f->T, C = f->C;
     const int64_t N = (int64_t)f->feature.size();
     std::vector<PNode> pn((size_t)N);
-    std::vector<double> leaf;
-    leaf.reserve((size_t)(N / 2 + T) * C);
-    std::vector<int64_t> roots(T);
-    std::vector<std::pair<int64_t, int64_t>> q;      // BFS queue of (flat index, device index)
-    int64_t next = 0, nleaf = 0;
-    for (int t = 0; t < T; t++) {
+    std::vector<int64_t> roots(T), leaf_base(T + 1, 0);
+    // trees are independent: count leaves per tree, then lay every tree out (BFS, children adjacent) in parallel
+    har::parallel_for(T, N > 4096, [&](int t) {
+        int64_t c = 0;
+        for (int64_t k = f->tree_off[t]; k < f->tree_off[t + 1]; k++) c += f->feature[k] < 0;
+        leaf_base[t + 1] = c;
+    });
+    for (int t = 0; t < T; t++) leaf_base[t + 1] += leaf_base[t];
+    std::vector<double> leaf((size_t)leaf_base[T] * C);
+    har::parallel_for(T, N > 4096, [&](int t) {
         const int64_t base = f->tree_off[t];
+        int64_t next = base, nleaf = leaf_base[t];
         roots[t] = next++;
-        q.clear();
+        std::vector<std::pair<int64_t, int64_t>> q;      // BFS queue of (flat index, device index)
+        q.reserve((size_t)(f->tree_off[t + 1] - base));
         q.emplace_back(base, roots[t]);
         for (size_t qi = 0; qi < q.size(); qi++) {
             const int64_t src = q[qi].first, dst = q[qi].second;
             PNode& d = pn[(size_t)dst];
             if (f->feature[src] < 0) {
-                d.feature = -1; d.left = (int32_t)nleaf++; d.thr = 0.0;
+                d.feature = -1; d.left = (int32_t)nleaf; d.thr = 0.0;
                 const double* st = &f->stats[(size_t)src * C];
+                double* lv = &leaf[(size_t)nleaf * C];
+                nleaf++;
                 double total = 0.0;
                 for (int c = 0; c < C; c++) total += st[c];
-                for (int c = 0; c < C; c++) leaf.push_back(is_forest ? (total != 0.0 ? st[c] / total : 0.0) : st[c]);
+                for (int c = 0; c < C; c++) lv[c] = is_forest ? (total != 0.0 ? st[c] / total : 0.0) : st[c];
             } else {
                 const int ar = f->arity[src];
                 d.feature = f->feature[src];
@@ -140,7 +148,7 @@ int build_device_tables(har_forest* f, int is_forest, cudaStream_t s) {
                 next += 2;
             }
         }
-    }
+    });
     har::pool_setup();
     HAR_CUDA(cudaMallocAsync(&f->d_nodes, sizeof(PNode) * std::max<int64_t>(N, 1), s));
     HAR_CUDA(cudaMallocAsync((void**)&f->d_leaf, sizeof(double) * std::max<size_t>(leaf.size(), 1), s));

@@ -344,18 +344,36 @@ struct Pinned {
 
 struct GroupItem { int tree; int node; };
 
-// Small fork-join helper for the host-side (driver) work; `go` = false runs inline.
-template <typename Fn>
-void parallel_for(int n, bool go, Fn fn) {
-    unsigned hw = std::thread::hardware_concurrency();
-    int nt = (int)std::min<unsigned>(hw ? hw : 1, 8);
-    if (!go || nt <= 1 || n < 2) { for (int i = 0; i < n; i++) fn(i); return; }
-    nt = std::min(nt, n);
-    std::vector<std::thread> th;
-    th.reserve(nt);
-    for (int k = 0; k < nt; k++) th.emplace_back([=, &fn] { for (int i = k; i < n; i += nt) fn(i); });
-    for (auto& t : th) t.join();
-}
+// A second stream forked from / joined into the caller's stream with events (created on first use).
+struct SideStream {
+    cudaStream_t s = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool active = false;
+    ~SideStream() {
+        if (active) cudaStreamSynchronize(s);
+        if (ev_fork) cudaEventDestroy(ev_fork);
+        if (ev_join) cudaEventDestroy(ev_join);
+        if (s) cudaStreamDestroy(s);
+    }
+    cudaError_t fork(cudaStream_t main) {
+        cudaError_t e;
+        if (!s) {
+            if ((e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)) != cudaSuccess) return e;
+            if ((e = cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming)) != cudaSuccess) return e;
+            if ((e = cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming)) != cudaSuccess) return e;
+        }
+        if ((e = cudaEventRecord(ev_fork, main)) != cudaSuccess) return e;
+        active = true;
+        return cudaStreamWaitEvent(s, ev_fork, 0);
+    }
+    cudaError_t join(cudaStream_t main) {
+        if (!active) return cudaSuccess;
+        cudaError_t e = cudaEventRecord(ev_join, s);
+        if (e != cudaSuccess) return e;
+        active = false;
+        return cudaStreamWaitEvent(main, ev_join, 0);
+    }
+};
 
 }  // namespace
 
@@ -474,6 +492,30 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         return fail(HAR_E_INVALID, "Classifier given dataset with invalid label %g.  Labels must be integers in range [0, %d).", v, C);
     }
 
+    // Bagging depends only on (n, T, seed, partitions): its serial-RNG kernel (a few dozen warps) runs on a side
+    // stream while split finding and binning use the rest of the GPU on the caller's stream.
+    const bool need_w = d_weights_in || !(T == 1 && p->subsampling_rate == 1.0);
+    DevBuf<uint8_t> d_wbuf;
+    DevBuf<int64_t> d_po;
+    const uint8_t* d_w = d_weights_in;
+    SideStream side;
+    if (need_w && !d_weights_in && n > 0) {
+        HAR_CUDA(d_wbuf.alloc((size_t)T * n, s));
+        d_w = d_wbuf.p;
+        if (T == 1 && p->subsampling_rate == 1.0) {
+            HAR_CUDA(cudaMemsetAsync(d_wbuf.p, 1, (size_t)n, s));
+        } else {
+            HAR_CUDA(d_po.alloc(num_parts + 1, s));
+            HAR_CUDA(cudaMemcpyAsync(d_po.p, part_off, sizeof(int64_t) * (num_parts + 1), cudaMemcpyHostToDevice, s));
+            HAR_CUDA(side.fork(s));                      // side stream waits for the allocations / copy above
+            prof_begin(side.s);
+            k_bag_weights<<<(unsigned)ceil_div(num_parts, 32), 32, 0, side.s>>>(n, T, p->subsampling_rate, std::exp(-p->subsampling_rate),
+                                                                                 p->seed, d_po.p, num_parts, part_offset, T > 1 ? 1 : 0, d_wbuf.p);
+            HAR_LAUNCH_CHECK();
+            prof_end(PROF_BAG, side.s, (double)n * T);
+        }
+    }
+
     std::unique_ptr<har_forest> fo(new har_forest());
     fo->T = T; fo->C = C; fo->F = F; fo->max_bins = MB; fo->max_depth = p->max_depth;
     fo->thresholds.assign((size_t)F * MB, 0.0);
@@ -491,15 +533,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     if (ldb != F) HAR_CUDA(cudaMemsetAsync(d_bins.p, 0, (size_t)std::max<int64_t>(n, 1) * ldb, s));   // zero padding bytes
     if (int rc = bin_features_impl(d_X, n, F, ld, arity, fo->thresholds.data(), fo->nsplits.data(), MB, d_bins.p, ldb, s)) return rc;
 
-    // bagging weights
-    const bool need_w = d_weights_in || !(T == 1 && p->subsampling_rate == 1.0);
-    DevBuf<uint8_t> d_wbuf;
-    const uint8_t* d_w = d_weights_in;
-    if (need_w && !d_weights_in) {
-        HAR_CUDA(d_wbuf.alloc((size_t)T * std::max<int64_t>(n, 1), s));
-        if (int rc = bag_weights_impl(n, T, p->subsampling_rate, p->seed, part_off, num_parts, part_offset, d_wbuf.p, s)) return rc;
-        d_w = d_wbuf.p;
-    }
+    HAR_CUDA(side.join(s));                              // weights are needed from here on
 
     // row permutations
     DevBuf<int32_t> perm0, perm1, d_cnt, d_chunk;
@@ -790,24 +824,29 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         if (trace) fprintf(stderr, "[har_forest_fit]   toNode: parallel emit %.2f ms\n", ms_since(t_emit));
         size_t total_nodes = 0;
         for (int t = 0; t < T; t++) { fo->tree_off[t] = (int64_t)total_nodes; total_nodes += parts[t].feature.size(); }
-        fo->feature.reserve(total_nodes); fo->left.reserve(total_nodes); fo->right.reserve(total_nodes);
-        fo->node_id.reserve(total_nodes); fo->arity.reserve(total_nodes); fo->threshold.reserve(total_nodes);
-        fo->left_mask.reserve(total_nodes); fo->prediction.reserve(total_nodes); fo->impurity.reserve(total_nodes);
-        fo->gain.reserve(total_nodes); fo->stats.reserve(total_nodes * C);
-        for (int t = 0; t < T; t++) {
-            const har_forest& pf = parts[t];
-            fo->feature.insert(fo->feature.end(), pf.feature.begin(), pf.feature.end());
-            fo->left.insert(fo->left.end(), pf.left.begin(), pf.left.end());
-            fo->right.insert(fo->right.end(), pf.right.begin(), pf.right.end());
-            fo->node_id.insert(fo->node_id.end(), pf.node_id.begin(), pf.node_id.end());
-            fo->arity.insert(fo->arity.end(), pf.arity.begin(), pf.arity.end());
-            fo->threshold.insert(fo->threshold.end(), pf.threshold.begin(), pf.threshold.end());
-            fo->left_mask.insert(fo->left_mask.end(), pf.left_mask.begin(), pf.left_mask.end());
-            fo->prediction.insert(fo->prediction.end(), pf.prediction.begin(), pf.prediction.end());
-            fo->impurity.insert(fo->impurity.end(), pf.impurity.begin(), pf.impurity.end());
-            fo->gain.insert(fo->gain.end(), pf.gain.begin(), pf.gain.end());
-            fo->stats.insert(fo->stats.end(), pf.stats.begin(), pf.stats.end());
-        }
+        // one host thread per output array: the first touch of the fresh allocations (page faults) and the copies
+        // run in parallel instead of serialising ~12 MB of inserts
+        har_forest* fp = fo.get();
+        auto cat = [&](auto har_forest::*member, size_t per_node) {
+            auto& dst = fp->*member;
+            dst.reserve(total_nodes * per_node);
+            for (int t = 0; t < T; t++) { const auto& src = parts[t].*member; dst.insert(dst.end(), src.begin(), src.end()); }
+        };
+        parallel_for(11, true, [&](int k) {
+            switch (k) {
+                case 0: cat(&har_forest::stats, (size_t)C); break;
+                case 1: cat(&har_forest::feature, 1); break;
+                case 2: cat(&har_forest::left, 1); break;
+                case 3: cat(&har_forest::right, 1); break;
+                case 4: cat(&har_forest::node_id, 1); break;
+                case 5: cat(&har_forest::arity, 1); break;
+                case 6: cat(&har_forest::threshold, 1); break;
+                case 7: cat(&har_forest::left_mask, 1); break;
+                case 8: cat(&har_forest::prediction, 1); break;
+                case 9: cat(&har_forest::impurity, 1); break;
+                default: cat(&har_forest::gain, 1); break;
+            }
+        });
     }
     fo->tree_off[T] = (int64_t)fo->feature.size();
     fo->num_launches = launches_since_reset() - launches0;
