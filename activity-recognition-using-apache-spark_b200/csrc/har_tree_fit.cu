@@ -10,6 +10,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
+#include <deque>
 #include <memory>
 #include <thread>
 
@@ -209,6 +210,25 @@ int bin_features_impl(const double* d_X, int64_t n, int F, int64_t ld, const int
     return HAR_OK;
 }
 
+// BaggedPoint.convertToBaggedRDD: Poisson(rate) with replacement when numTrees > 1, else Bernoulli(rate)
+int launch_bag(int64_t n, int T, double rate, int64_t seed, const int64_t* d_part_off, int num_parts, int partition_offset,
+               uint8_t* d_w, cudaStream_t s) {
+    static const bool v1 = [] { const char* e = std::getenv("HAR_BAG_KERNEL"); return e && std::string(e) == "v1"; }();
+    const unsigned grid = (unsigned)ceil_div(num_parts, 32);
+    if (T > 1 && !v1) {
+        const double lim = std::ceil(1000.0 * rate);
+        const int ilimit = lim >= 2147483647.0 ? 2147483647 : (int)lim;
+        const size_t smem = BAG_SMEM_BYTES;
+        HAR_CUDA(cudaFuncSetAttribute(k_bag_poisson, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_bag_poisson<<<grid, BAG_THREADS, smem, s>>>(n, T, std::exp(-rate), ilimit, seed, d_part_off, num_parts, partition_offset, d_w);
+    } else {
+        k_bag_weights<<<grid, 32, 0, s>>>(n, T, rate, std::exp(-rate), seed, d_part_off, num_parts, partition_offset,
+                                          T > 1 ? 1 : 0, d_w);
+    }
+    HAR_LAUNCH_CHECK();
+    return HAR_OK;
+}
+
 int bag_weights_impl(int64_t n, int T, double rate, int64_t seed, const int64_t* part_off, int num_parts,
                      int partition_offset, uint8_t* d_w, cudaStream_t s) {
     if (n == 0) return HAR_OK;
@@ -217,9 +237,7 @@ int bag_weights_impl(int64_t n, int T, double rate, int64_t seed, const int64_t*
     HAR_CUDA(d_po.alloc(num_parts + 1, s));
     HAR_CUDA(cudaMemcpyAsync(d_po.p, part_off, sizeof(int64_t) * (num_parts + 1), cudaMemcpyHostToDevice, s));
     prof_begin(s);
-    k_bag_weights<<<(unsigned)ceil_div(num_parts, 32), 32, 0, s>>>(n, T, rate, std::exp(-rate), seed, d_po.p, num_parts,
-                                                                   partition_offset, T > 1 ? 1 : 0, d_w);
-    HAR_LAUNCH_CHECK();
+    if (int rc = launch_bag(n, T, rate, seed, d_po.p, num_parts, partition_offset, d_w, s)) return rc;
     prof_end(PROF_BAG, s, (double)n * T);
     HAR_CUDA(cudaStreamSynchronize(s));       // part_off is a caller buffer
     return HAR_OK;
@@ -283,7 +301,34 @@ struct LNode {
     int64_t start = 0;
     int32_t count = 0;
     int buf = 0;
+    // sibling subtraction: the node's parent, its position in the batch being assembled, and (for a split node whose
+    // two children both go on) the kept all-reduced counters until both children have been processed
+    int parent = -1;
+    int batch_pos = -1;
+    int64_t batch_stamp = -1;
+    uint32_t* kept = nullptr;
+    int kids_pending = 0;
     std::vector<int32_t> subset;
+};
+
+// Device slots for kept parent counters ([hist_len] + [C] words each), carved from slabs that live until the fit ends.
+struct HistStore {
+    size_t slot_words = 0;
+    std::deque<DevBuf<uint32_t>> slabs;
+    std::vector<uint32_t*> free_slots;
+    cudaError_t get(uint32_t** out, cudaStream_t s) {
+        if (free_slots.empty()) {
+            const size_t per = std::max<size_t>(64, (size_t(64) << 20) / (slot_words * 4));   // 64 MB slabs
+            slabs.emplace_back();
+            cudaError_t e = slabs.back().alloc(per * slot_words, s);
+            if (e != cudaSuccess) { slabs.pop_back(); return e; }
+            for (size_t i = per; i-- > 0;) free_slots.push_back(slabs.back().p + i * slot_words);
+        }
+        *out = free_slots.back();
+        free_slots.pop_back();
+        return cudaSuccess;
+    }
+    void put(uint32_t* p) { free_slots.push_back(p); }
 };
 int level_of(int id) { int l = 0; while (id > 1) { id >>= 1; l++; } return l; }
 int first_argmax(const uint32_t* s, int C) {
@@ -418,7 +463,7 @@ HAR_API int har_node_histogram(const uint8_t* d_bins, int64_t ldb, const uint8_t
             return fail(HAR_E_UNSUPPORTED, "feature %d needs %d counters; tile limit is %d", f, loff[f + 1] - loff[f], HIST_TILE_WORDS);
     const int chunk_rows = 2048;
     NodeDesc nd{};
-    nd.start = 0; nd.hist_base = 0; nd.count = (int32_t)nrows; nd.tree = 0; nd.buf = 0; nd.level = 0; nd.sub_off = 0;
+    nd.start = 0; nd.hist_base = 0; nd.count = (int32_t)nrows; nd.tree = 0; nd.buf = 0; nd.level = 0; nd.sub_off = 0; nd.sib = -1;
     nd.nf = F; nd.hist_len = loff[F];
     int32_t item_off[2] = {0, (int32_t)ceil_div(nrows, chunk_rows)};
     DevBuf<NodeDesc> d_nd; DevBuf<int32_t> d_io, d_loff; DevBuf<uint8_t> d_kind;
@@ -509,9 +554,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             HAR_CUDA(cudaMemcpyAsync(d_po.p, part_off, sizeof(int64_t) * (num_parts + 1), cudaMemcpyHostToDevice, s));
             HAR_CUDA(side.fork(s));                      // side stream waits for the allocations / copy above
             prof_begin(side.s);
-            k_bag_weights<<<(unsigned)ceil_div(num_parts, 32), 32, 0, side.s>>>(n, T, p->subsampling_rate, std::exp(-p->subsampling_rate),
-                                                                                 p->seed, d_po.p, num_parts, part_offset, T > 1 ? 1 : 0, d_wbuf.p);
-            HAR_LAUNCH_CHECK();
+            if (int rc = launch_bag(n, T, p->subsampling_rate, p->seed, d_po.p, num_parts, part_offset, d_wbuf.p, side.s)) return rc;
             prof_end(PROF_BAG, side.s, (double)n * T);
         }
     }
@@ -594,8 +637,16 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     // page-locked staging, kept across fits (cudaMallocHost is far too slow to repeat per call)
     static thread_local Pinned<NodeDesc> h_nodes;
     static thread_local Pinned<NodeResult> h_res;
-    static thread_local Pinned<int32_t> h_item_off, h_sub;
+    static thread_local Pinned<int32_t> h_item_off, h_hitem_off, h_sub;
+    DevBuf<int32_t> d_hitem_off;
     size_t cap_nodes = 0, cap_hist = 0, cap_items = 0, cap_sub = 0;
+    // sibling subtraction (all-features fits only: with per-node feature subsets parent and child count different features)
+    bool subtract = !subsample;
+    if (const char* e = std::getenv("HAR_HIST_SUBTRACT")) subtract = subtract && std::atoi(e) != 0;
+    HistStore store;
+    store.slot_words = (size_t)full_len + C;
+    std::vector<uint32_t*> group_slot;                      // per node of the group: the slot its counters may be kept in
+    int64_t batch_stamp = 0;
     if (!subsample) {
         HAR_CUDA(d_loff_all.alloc(F + 1, s));
         HAR_CUDA(cudaMemcpyAsync(d_loff_all.p, m.loff.data(), sizeof(int32_t) * (F + 1), cudaMemcpyHostToDevice, s));
@@ -639,6 +690,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         const NodeResult* res_ptr = nullptr;
 
         // ---- findBestSplits, in device batches bounded by the counter budget ----
+        if (subtract) group_slot.assign(ng_total, nullptr);
         int64_t g0 = 0;
         while (g0 < ng_total) {
             int64_t g1 = g0, words = 0, rows_total = 0;
@@ -659,12 +711,49 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             // host-side descriptors
             HAR_CUDA(h_nodes.reserve(ng)); HAR_CUDA(h_item_off.reserve(ng + 1)); HAR_CUDA(h_res.reserve(ng));
             if (subsample) HAR_CUDA(h_sub.reserve((size_t)ng * (K + 1) * 2));
-            int64_t hb = 0, items = 0;
+            HAR_CUDA(h_hitem_off.reserve(ng + 1));
+            // sibling subtraction: pair up children whose parent's counters were kept and that sit in this batch;
+            // the child with fewer weighted instances (global class totals, so every rank picks the same one) is
+            // accumulated from rows, the other derived.  Counter layout of the batch buffer:
+            //   [accumulated nodes][class totals of all nodes][derived nodes]   (memset / all-reduce cover the first two)
+            batch_stamp++;
+            int n_derived = 0;
+            if (subtract) {
+                for (int g = 0; g < ng; g++) {
+                    LNode& nd = trees[group[g0 + g].tree][group[g0 + g].node];
+                    nd.batch_pos = g; nd.batch_stamp = batch_stamp;
+                }
+            }
+            auto weight_of = [&](int t, int ni) {
+                uint64_t w = 0;
+                for (int c = 0; c < C; c++) w += tree_stats[t][(size_t)ni * C + c];
+                return w;
+            };
+            for (int g = 0; g < ng; g++) {                          // who is derived, who may be kept
+                NodeDesc& d = h_nodes.p[g];
+                d.sib = -1; d.from = nullptr; d.save = nullptr;
+                if (!subtract) continue;
+                const int t = group[g0 + g].tree, ni = group[g0 + g].node;
+                const LNode& nd = trees[t][ni];
+                if (level_of(nd.id) + 1 < p->max_depth) {          // its children can still be split: counters may be kept
+                    HAR_CUDA(store.get(&group_slot[g0 + g], s));
+                    d.save = group_slot[g0 + g];
+                }
+                if (nd.parent < 0) continue;
+                const LNode& par = trees[t][nd.parent];
+                if (!par.kept) continue;
+                const LNode& sb = trees[t][par.left == ni ? par.right : par.left];
+                if (sb.batch_stamp != batch_stamp) continue;
+                const int derived_child = weight_of(t, par.left) <= weight_of(t, par.right) ? par.right : par.left;
+                if (derived_child == ni) { d.sib = sb.batch_pos; d.from = par.kept; n_derived++; }
+            }
+            int64_t hb = 0, items = 0, hitems = 0, hist_rows = 0;
+            int64_t derived_base = (int64_t)(ng - n_derived) * full_len + (int64_t)ng * C;   // used when !subsample
             for (int g = 0; g < ng; g++) {
                 const LNode& nd = trees[group[g0 + g].tree][group[g0 + g].node];
                 NodeDesc& d = h_nodes.p[g];
-                d.start = nd.start; d.hist_base = hb; d.count = nd.count; d.tree = group[g0 + g].tree; d.buf = nd.buf;
-                d.level = level_of(nd.id); d.pad = 0;
+                d.start = nd.start; d.count = nd.count; d.tree = group[g0 + g].tree; d.buf = nd.buf;
+                d.level = level_of(nd.id);
                 if (subsample) {
                     d.sub_off = g * (K + 1); d.nf = K;
                     int32_t* fl = h_sub.p + (size_t)g * (K + 1);
@@ -674,18 +763,25 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                     fl[K] = 0; lo[K] = off;
                     d.hist_len = off;
                 } else { d.sub_off = 0; d.nf = F; d.hist_len = (int32_t)full_len; }
-                hb += d.hist_len;
+                if (d.sib < 0) { d.hist_base = hb; hb += d.hist_len; }
+                else { d.hist_base = derived_base; derived_base += d.hist_len; }
                 h_item_off.p[g] = (int32_t)items;
                 items += ceil_div(nd.count, chunk_rows);
+                h_hitem_off.p[g] = (int32_t)hitems;
+                if (d.sib < 0) { hitems += ceil_div(nd.count, chunk_rows); hist_rows += nd.count; }
             }
             h_item_off.p[ng] = (int32_t)items;
+            h_hitem_off.p[ng] = (int32_t)hitems;
+            // [0, hb): accumulated counters; [hb, hb + ng*C): class totals; then the derived nodes' counters
+            const size_t reduce_words = (size_t)hb + (size_t)ng * C;
+            const size_t need_hist = reduce_words + (size_t)n_derived * full_len;
             if (items > 0x7fffffff) return fail(HAR_E_UNSUPPORTED, "too many work items in one batch");
             // device buffers (grow-only)
             if ((size_t)ng > cap_nodes) {
                 cap_nodes = (size_t)ng * 2;
                 HAR_CUDA(d_nodes.alloc(cap_nodes, s)); HAR_CUDA(d_res.alloc(cap_nodes, s)); HAR_CUDA(d_item_off.alloc(cap_nodes + 1, s));
+                HAR_CUDA(d_hitem_off.alloc(cap_nodes + 1, s));
             }
-            const size_t need_hist = (size_t)hb + (size_t)ng * C;
             if (need_hist > cap_hist) { cap_hist = need_hist + need_hist / 4; HAR_CUDA(d_hist.alloc(cap_hist, s)); }
             if ((size_t)items + 1 > cap_items) { cap_items = (size_t)items * 2 + 1; HAR_CUDA(d_chunk_left.alloc(cap_items, s)); }
             if (subsample && (size_t)ng * (K + 1) * 2 > cap_sub) {
@@ -701,25 +797,35 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             }
             HAR_CUDA(cudaMemcpyAsync(d_nodes.p, h_nodes.p, sizeof(NodeDesc) * ng, cudaMemcpyHostToDevice, s));
             HAR_CUDA(cudaMemcpyAsync(d_item_off.p, h_item_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, s));
-            HAR_CUDA(cudaMemsetAsync(d_hist.p, 0, sizeof(uint32_t) * need_hist, s));
+            HAR_CUDA(cudaMemcpyAsync(d_hitem_off.p, h_hitem_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, s));
+            HAR_CUDA(cudaMemsetAsync(d_hist.p, 0, sizeof(uint32_t) * reduce_words, s));
             uint32_t* d_parent = d_hist.p + hb;
-            if (items > 0) {
+            if (hitems > 0) {
                 prof_begin(s);
                 if (subsample)
-                    k_node_hist<true><<<(unsigned)items, HIST_THREADS, hist_smem, s>>>(d_nodes.p, d_item_off.p, ng, chunk_rows, d_bins.p, ldb,
+                    k_node_hist<true><<<(unsigned)hitems, HIST_THREADS, hist_smem, s>>>(d_nodes.p, d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
                         d_lab.p, d_w, n, perm0.p, perm1.p, flist_p, loff_p, d_kind.p, C, d_hist.p, d_parent);
                 else
-                    k_node_hist<false><<<(unsigned)items, HIST_THREADS, hist_smem, s>>>(d_nodes.p, d_item_off.p, ng, chunk_rows, d_bins.p, ldb,
+                    k_node_hist<false><<<(unsigned)hitems, HIST_THREADS, hist_smem, s>>>(d_nodes.p, d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
                         d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, d_hist.p, d_parent);
                 HAR_LAUNCH_CHECK();
-                prof_end(PROF_NODE_HIST, s, (double)rows_total);
+                prof_end(PROF_NODE_HIST, s, (double)hist_rows);
             }
             // the only exchange on the path: reduceByKey(_.merge(_)) -> all-reduce of the batch's counters
-            if (int rc = dist_allreduce(dist, d_hist.p, (int64_t)need_hist, s)) return rc;
+            if (int rc = dist_allreduce(dist, d_hist.p, (int64_t)reduce_words, s)) return rc;
+            const unsigned copy_slices = (unsigned)std::max<int64_t>(1, std::min<int64_t>(8, full_len / 2048));
+            if (n_derived > 0) {
+                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, s>>>(d_nodes.p, C, d_hist.p, d_parent);
+                HAR_LAUNCH_CHECK();
+            }
             prof_begin(s);
             k_best_split<<<ng, BS_THREADS, bs_smem, s>>>(d_nodes.p, ng, d_hist.p, d_parent, flist_p, loff_p, subsample ? 1 : 0, fm, d_res.p);
             HAR_LAUNCH_CHECK();
             prof_end(PROF_BEST_SPLIT, s, (double)ng);
+            if (subtract && !all_last_level) {
+                k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, s>>>(d_nodes.p, d_res.p, C, d_hist.p, d_parent);
+                HAR_LAUNCH_CHECK();
+            }
             if (!all_last_level && items > 0) {
                 prof_begin(s);
                 k_part_count<<<(unsigned)items, HIST_THREADS, 0, s>>>(d_nodes.p, d_item_off.p, ng, chunk_rows, d_res.p, d_bins.p, ldb, n,
@@ -760,6 +866,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         }
         std::vector<int> torder = scala_hashmap_order(tkeys);
         std::vector<std::vector<int>> by_tree(T), pushes(T);
+        std::vector<std::vector<uint32_t*>> released(T);
         for (int g = 0; g < (int)ng_total; g++) by_tree[group[g].tree].push_back(g);
         auto process_tree = [&](int t) {
             std::vector<LNode>& tr = trees[t];
@@ -771,13 +878,18 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 const int ni = group[g].node;
                 const int level = level_of(tr[ni].id);
                 const bool is_leaf = !(r.gain > 0.0) || level == p->max_depth;
+                uint32_t* slot = subtract ? group_slot[g] : nullptr;
                 {
                     LNode& nd = tr[ni];
+                    if (nd.parent >= 0) {                           // this child is done: drop the parent's kept counters after both
+                        LNode& par = tr[nd.parent];
+                        if (par.kept && --par.kids_pending == 0) { released[t].push_back(par.kept); par.kept = nullptr; }
+                    }
                     nd.is_leaf = is_leaf; nd.valid = r.valid != 0; nd.gain = r.gain; nd.impurity = r.impurity;
                     for (int c = 0; c < C; c++) ts[(size_t)ni * C + c] = r.parent[c];
                     if (!nd.subset.empty()) std::vector<int32_t>().swap(nd.subset);
                 }
-                if (is_leaf) continue;
+                if (is_leaf) { if (slot) released[t].push_back(slot); continue; }
                 const bool child_leaf = level + 1 == p->max_depth;
                 const bool ll = child_leaf || r.left_imp == 0.0, rl = child_leaf || r.right_imp == 0.0;
                 const bool parted = !(ll && rl);
@@ -786,6 +898,11 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 LNode& nd = tr[ni];
                 LNode& L = tr[li]; LNode& R = tr[li + 1];
                 L.id = nd.id * 2; R.id = L.id + 1;
+                L.parent = R.parent = ni;
+                if (slot) {
+                    if (r.retain) { nd.kept = slot; nd.kids_pending = 2; }
+                    else released[t].push_back(slot);
+                }
                 L.is_leaf = ll; R.is_leaf = rl; L.impurity = r.left_imp; R.impurity = r.right_imp;
                 ts.resize((size_t)(li + 2) * C);
                 for (int c = 0; c < C; c++) { ts[(size_t)li * C + c] = r.left[c]; ts[(size_t)(li + 1) * C + c] = r.right[c]; }
@@ -802,6 +919,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         for (int oi : torder) {
             const int t = tkeys[oi];
             for (int ni : pushes[t]) stack.push_back({t, ni});
+            for (uint32_t* sl : released[t]) store.put(sl);
         }
         t_post += ms_since(t_a);
     }

@@ -360,7 +360,15 @@ def run_ours(args):
         "seg_tiles": 8,                     # per sample: user + activity i32
         "predict": F * 8 + 104,             # per row: 43 f64 read + raw/prob/pred written
         "part_count": 4 + 1, "part_scatter": 4 + 1 + 4,
-        "bin_features": F * 8 + F}
+        "bin_features": F * 8 + F,
+        "bag_weights": 1,                   # per (row, tree): one weight byte written
+        "best_split": (F * 32 * 6 + 6) * 4 + 456}   # per node: its counters read once + one result record written
+    limiter = {
+        "node_hist": "shared-memory atomics (red.shared.add.u32), not HBM",
+        "bag_weights": "one serial Well19937c stream per Spark partition (latency chain of the generator), not HBM; "
+                       "runs on a side stream under split finding and binning",
+        "best_split": "fp64 gini evaluation of every (feature, threshold) candidate (issue-bound), not HBM",
+        "window_features": "issue/latency-bound (ncu: no pipe or memory unit above 60 %), see profiles/"}
     dominant = max(kern, key=lambda k: kern[k]["ms_per_step"]) if kern else None
     roofs = {}
     for name, k in kern.items():
@@ -376,9 +384,10 @@ def run_ours(args):
     roofline = dict(roofs.get(dominant, {}))
     roofline["kernel"] = dominant
     roofline["peak_source"] = peak_src
+    if dominant in limiter:
+        roofline["limiter"] = limiter[dominant]
     if dominant == "node_hist":
         k = kern["node_hist"]
-        roofline["limiter"] = "shared-memory atomics (red.shared.add.u32), not HBM"
         roofline["smem_atomics_per_s"] = k["units_per_step"] * F / (k["ms_per_step"] * 1e-3)
         try:       # measured micro-benchmark peaks of red.shared.add.u32 on this GPU (same tile size as the kernel)
             pk_free, pk_rand = core.smem_atomic_peak(0), core.smem_atomic_peak(1)

@@ -160,6 +160,29 @@ def test_node_group_split_into_several_device_batches(monkeypatch):
     assert_forest_equal(ref, g)
 
 
+def test_sibling_subtraction_changes_nothing(monkeypatch):
+    """With all features per node the larger child's counters are derived as parent - sibling; the forest
+    must be the one obtained by accumulating every node from its rows (HAR_HIST_SUBTRACT=0), with mixed
+    continuous / unordered / ordered features and a max_memory_bytes that splits sibling pairs over groups."""
+    from har_b200 import core
+    X, y, arity = synth_tree_data(20000, F=14, C=5, seed=17, n_cat_unordered=2, n_cat_ordered=2)
+    kw = dict(arity=arity, num_classes=5, num_trees=6, max_depth=8, feature_subset="all", seed=4, max_bins=32)
+    g = core.fit_forest(X, y, **kw)
+    small = core.fit_forest(X, y, max_memory_mb=1, **kw)        # ~70 nodes per group: pairs straddle groups
+    single = core.fit_forest(X, y, max_memory_mb=0, **kw)       # one node per group: nothing can be derived
+    monkeypatch.setenv("HAR_HIST_SUBTRACT", "0")
+    plain = core.fit_forest(X, y, **kw)
+    plain_small = core.fit_forest(X, y, max_memory_mb=1, **kw)
+    o = orc.fit_forest(X, y, **kw)
+    o_small = orc.fit_forest(X, y, max_memory_mb=1, **kw)
+    assert_forest_equal(plain, g)
+    assert_forest_equal(o, g)
+    assert small.num_groups > 2 * g.num_groups
+    assert_forest_equal(plain_small, small)
+    assert_forest_equal(o_small, small)
+    assert single.num_groups > 4 * small.num_groups and single.total_nodes == plain_small.total_nodes
+
+
 def test_entropy_forest_same_structure():
     """Entropy uses log(); CUDA's and glibc's may differ in the last ulp, so gains are compared to 1e-12
     and the structure must still be identical on this data (documented caveat in DESIGN.md)."""
