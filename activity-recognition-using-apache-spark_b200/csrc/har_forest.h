@@ -1,6 +1,8 @@
 // The opaque har_forest handle: flat host copy of the (pruned) trees + lazily built device tables.
 #pragma once
 #include <cstdint>
+#include <functional>
+#include <mutex>
 #include <vector>
 
 struct har_forest {
@@ -14,7 +16,12 @@ struct har_forest {
     std::vector<double> thresholds;
     std::vector<int32_t> nsplits;
     int max_bins = 0;
-    int64_t num_groups = 0, num_batches = 0, num_launches = 0;
+    mutable int64_t num_groups = 0;
+    int64_t num_batches = 0, num_launches = 0;
+    // when the fit trained its nodes in another order than Spark's (see har_tree_fit.cu), the number of Spark node
+    // groups is recounted from the finished trees the first time har_forest_fit_info asks for it
+    mutable std::function<int64_t()> count_groups;
+    mutable std::mutex count_mu;
     // device tables for predict (built on first use, on the device current at that time)
     int dev = -1;
     void* d_nodes = nullptr;      // PNode[total]

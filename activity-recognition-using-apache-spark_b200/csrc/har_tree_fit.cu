@@ -304,6 +304,9 @@ struct LNode {
     // sibling subtraction: the node's parent, its position in the batch being assembled, and (for a split node whose
     // two children both go on) the kept all-reduced counters until both children have been processed
     int parent = -1;
+    int level = 0;                  // depth of the node (root 0)
+    bool pushed = true;             // went onto the node stack when it was created (not a leaf by depth or purity)
+    bool derive_pref = false;       // of a sibling pair, the child with more weighted instances: derived when both are in a batch
     int batch_pos = -1;
     int64_t batch_stamp = -1;
     uint32_t* kept = nullptr;
@@ -335,6 +338,46 @@ int first_argmax(const uint32_t* s, int C) {
     int b = -1; uint32_t mv = 0;
     for (int c = 0; c < C; c++) if (b < 0 || s[c] > mv) { b = c; mv = s[c]; }
     return b;
+}
+
+struct GroupItem { int tree; int node; };
+
+// Number of node groups RandomForest.run would have formed for finished trees whose nodes all cost the same
+// (all features per node): replays the LIFO node stack, the memory-bounded selectNodesToSplit and the
+// per-group push order (Scala mutable.HashMap order of the tree indices, pop order inside a tree).
+int64_t simulate_groups(const std::vector<std::vector<LNode>>& trees, int64_t cost, int64_t max_memory) {
+    const int T = (int)trees.size();
+    std::vector<GroupItem> stack, group;
+    for (int t = 0; t < T; t++) stack.push_back({t, 0});
+    std::vector<std::vector<int>> pushes(T);
+    std::vector<char> seen(T, 0);
+    std::vector<int> tkeys;
+    int64_t groups = 0;
+    while (!stack.empty()) {
+        group.clear();
+        int64_t mem = 0;
+        while (!stack.empty()) {
+            if (mem + cost <= max_memory || mem == 0) { group.push_back(stack.back()); stack.pop_back(); mem += cost; }
+            else break;
+        }
+        groups++;
+        tkeys.clear();
+        for (auto& gi : group) if (!seen[gi.tree]) { seen[gi.tree] = 1; tkeys.push_back(gi.tree); }
+        for (auto& gi : group) {
+            const LNode& nd = trees[gi.tree][gi.node];
+            if (nd.left < 0) continue;
+            if (trees[gi.tree][nd.left].pushed) pushes[gi.tree].push_back(nd.left);
+            if (trees[gi.tree][nd.right].pushed) pushes[gi.tree].push_back(nd.right);
+        }
+        const std::vector<int> torder = scala_hashmap_order(tkeys);
+        for (int oi : torder) {
+            const int t = tkeys[oi];
+            for (int ni : pushes[t]) stack.push_back({t, ni});
+            pushes[t].clear();
+            seen[t] = 0;
+        }
+    }
+    return groups;
 }
 
 // LearningNode.toNode(prune = true) into the flat pre-order layout
@@ -387,7 +430,6 @@ struct Pinned {
     }
 };
 
-struct GroupItem { int tree; int node; };
 
 // A second stream forked from / joined into the caller's stream with events (created on first use).
 struct SideStream {
@@ -598,7 +640,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     }
 
     // device-side metadata
-    DevBuf<uint8_t> d_kind; DevBuf<int32_t> d_nsplits, d_hbins, d_loff_all, d_flist_all;
+    DevBuf<uint8_t> d_kind; DevBuf<int32_t> d_nsplits, d_hbins, d_loff_all;
     HAR_CUDA(d_kind.alloc(F, s)); HAR_CUDA(d_nsplits.alloc(F, s)); HAR_CUDA(d_hbins.alloc(F, s));
     HAR_CUDA(cudaMemcpyAsync(d_kind.p, m.kind.data(), F, cudaMemcpyHostToDevice, s));
     HAR_CUDA(cudaMemcpyAsync(d_nsplits.p, m.num_splits.data(), sizeof(int32_t) * F, cudaMemcpyHostToDevice, s));
@@ -617,36 +659,20 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     // trees + node stack (RandomForest.run)
     std::vector<std::vector<LNode>> trees(T);
     std::vector<std::vector<uint32_t>> tree_stats(T);      // [node][C] class counts, kept out of the hot LNode
-    std::vector<GroupItem> stack;
     for (int t = 0; t < T; t++) {
         LNode r; r.id = 1; r.start = 0; r.count = root_cnt[t]; r.buf = 0;
         trees[t].reserve(256);
         trees[t].push_back(r);
         tree_stats[t].assign(C, 0);
-        stack.push_back({t, 0});
     }
     JavaRand rng(p->seed);
 
     // batch buffers
     int64_t budget_words = 96LL << 20;                       // 384 MB of counters per device batch
     if (const char* e = std::getenv("HAR_HIST_BUDGET_WORDS")) budget_words = std::max<int64_t>(1, std::atoll(e));   // tests
-    DevBuf<uint32_t> d_hist;
-    DevBuf<NodeDesc> d_nodes;
-    DevBuf<NodeResult> d_res;
-    DevBuf<int32_t> d_item_off, d_chunk_left;
-    // page-locked staging, kept across fits (cudaMallocHost is far too slow to repeat per call)
-    static thread_local Pinned<NodeDesc> h_nodes;
-    static thread_local Pinned<NodeResult> h_res;
-    static thread_local Pinned<int32_t> h_item_off, h_hitem_off, h_sub;
-    DevBuf<int32_t> d_hitem_off;
-    size_t cap_nodes = 0, cap_hist = 0, cap_items = 0, cap_sub = 0;
     // sibling subtraction (all-features fits only: with per-node feature subsets parent and child count different features)
     bool subtract = !subsample;
     if (const char* e = std::getenv("HAR_HIST_SUBTRACT")) subtract = subtract && std::atoi(e) != 0;
-    HistStore store;
-    store.slot_words = (size_t)full_len + C;
-    std::vector<uint32_t*> group_slot;                      // per node of the group: the slot its counters may be kept in
-    int64_t batch_stamp = 0;
     if (!subsample) {
         HAR_CUDA(d_loff_all.alloc(F + 1, s));
         HAR_CUDA(cudaMemcpyAsync(d_loff_all.p, m.loff.data(), sizeof(int32_t) * (F + 1), cudaMemcpyHostToDevice, s));
@@ -658,17 +684,60 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                            sizeof(Cand) * (BS_THREADS / 32 + 1) + 64;
     HAR_CUDA(cudaFuncSetAttribute(k_best_split, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
 
-    std::vector<GroupItem> group;
-    std::vector<NodeResult> group_res;
+    // ---- tree sets -----------------------------------------------------------------------------------
+    // With all features per node a node's split depends on nothing but its own rows, so the order in which
+    // nodes are trained is free (only the *count* of Spark node groups is observable; it is recomputed from the
+    // finished trees, see simulate_groups).  The trees are then dealt into two sets that run the
+    // selectNodesToSplit / findBestSplits loop independently and take turns on the one stream: while the GPU
+    // works on a batch of one set, the host does the driver-side bookkeeping and the descriptors of the other.
+    // With per-node feature subsets the pop order feeds the subset RNG, so there is one set and Spark's order.
+    struct PinnedScratch {
+        Pinned<NodeDesc> h_nodes; Pinned<NodeResult> h_res; Pinned<uint32_t> h_res_stats;
+        Pinned<int32_t> h_item_off, h_hitem_off, h_sub;
+    };
+    // page-locked staging, kept across fits (cudaMallocHost is far too slow to repeat per call)
+    static thread_local PinnedScratch pinned[2];
+    struct FitSet {
+        std::vector<GroupItem> stack, group;
+        std::vector<NodeResult> group_res;
+        std::vector<uint32_t> group_stats;
+        std::vector<uint32_t*> group_slot;                  // per node of the group: the slot its counters may be kept in
+        const NodeResult* res_ptr = nullptr;
+        const uint32_t* stat_ptr = nullptr;
+        int64_t ng_total = 0, g0 = 0, cur_g0 = 0;
+        int cur_ng = 0;
+        bool inflight = false, done = false;
+        DevBuf<uint32_t> d_hist, d_res_stats;               // d_res_stats: [node][left | right | parent][C]
+        DevBuf<NodeDesc> d_nodes;
+        DevBuf<NodeResult> d_res;
+        DevBuf<int32_t> d_item_off, d_hitem_off, d_chunk_left, d_flist_all;
+        size_t cap_nodes = 0, cap_hist = 0, cap_items = 0, cap_sub = 0;
+        HistStore store;
+        int64_t batch_stamp = 0;
+        PinnedScratch* pin = nullptr;
+        cudaEvent_t ev = nullptr;
+        ~FitSet() { if (ev) cudaEventDestroy(ev); }
+    };
+    int num_sets = (!subsample && T >= 2) ? 2 : 1;
+    if (const char* e = std::getenv("HAR_FIT_SETS")) num_sets = std::max(1, std::min(num_sets, std::atoi(e)));
+    FitSet sets[2];
+    for (int k = 0; k < num_sets; k++) {
+        sets[k].pin = &pinned[k];
+        sets[k].store.slot_words = (size_t)full_len + C;
+        HAR_CUDA(cudaEventCreateWithFlags(&sets[k].ev, cudaEventDisableTiming));
+    }
+    for (int t = 0; t < T; t++) sets[t % num_sets].stack.push_back({t, 0});
+    int64_t groups_run = 0;
+
     if (trace) cudaStreamSynchronize(s);
     const double t_setup = ms_since(t_begin);
-    while (!stack.empty()) {
-        auto t_a = now();
-        // ---- selectNodesToSplit ----
-        group.clear();
+
+    // ---- selectNodesToSplit ----
+    auto select_group = [&](FitSet& S) {
+        S.group.clear();
         int64_t mem = 0;
-        while (!stack.empty()) {
-            GroupItem top = stack.back();
+        while (!S.stack.empty()) {
+            GroupItem top = S.stack.back();
             std::vector<int32_t> subset;
             int64_t tb = total_bins_all;
             if (subsample) {
@@ -679,85 +748,82 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             }
             const int64_t cost = (int64_t)C * tb * 8;
             if (mem + cost <= p->max_memory_bytes || mem == 0) {
-                stack.pop_back();
+                S.stack.pop_back();
                 trees[top.tree][top.node].subset.swap(subset);
-                group.push_back(top);
+                S.group.push_back(top);
                 mem += cost;
             } else break;
         }
-        fo->num_groups++;
-        const int64_t ng_total = (int64_t)group.size();
-        const NodeResult* res_ptr = nullptr;
+        groups_run++;
+        S.ng_total = (int64_t)S.group.size();
+        S.res_ptr = nullptr; S.stat_ptr = nullptr;
+        if (subtract) S.group_slot.assign(S.ng_total, nullptr);
+        S.g0 = 0;
+    };
 
-        // ---- findBestSplits, in device batches bounded by the counter budget ----
-        if (subtract) group_slot.assign(ng_total, nullptr);
-        int64_t g0 = 0;
-        while (g0 < ng_total) {
-            int64_t g1 = g0, words = 0, rows_total = 0;
+    // ---- findBestSplits: enqueue one device batch of the set's group (bounded by the counter budget) ----
+    auto enqueue_batch = [&](FitSet& S) -> int {
+        auto t_a = now();
+        {
+            int64_t g1 = S.g0, words = 0, rows_total = 0;
             bool all_last_level = true;
-            while (g1 < ng_total) {
-                const LNode& nd = trees[group[g1].tree][group[g1].node];
+            while (g1 < S.ng_total) {
+                const LNode& nd = trees[S.group[g1].tree][S.group[g1].node];
                 int64_t len = full_len;
                 if (subsample) { len = 0; for (int f : nd.subset) len += (int64_t)m.hist_bins[f] * C; }
-                if (g1 > g0 && (words + len > budget_words || g1 - g0 >= (1 << 20))) break;
+                if (g1 > S.g0 && (words + len > budget_words || g1 - S.g0 >= (1 << 20))) break;
                 words += len; rows_total += nd.count;
-                if (level_of(nd.id) + 1 < p->max_depth) all_last_level = false;
+                if (nd.level + 1 < p->max_depth) all_last_level = false;
                 g1++;
             }
-            const int ng = (int)(g1 - g0);
+            const int ng = (int)(g1 - S.g0);
             fo->num_batches++;
             int chunk_rows = (int)std::min<int64_t>(4096, std::max<int64_t>(256, rows_total / (kNumSMs * 8)));
             chunk_rows = (chunk_rows + 255) & ~255;
             // host-side descriptors
-            HAR_CUDA(h_nodes.reserve(ng)); HAR_CUDA(h_item_off.reserve(ng + 1)); HAR_CUDA(h_res.reserve(ng));
-            if (subsample) HAR_CUDA(h_sub.reserve((size_t)ng * (K + 1) * 2));
-            HAR_CUDA(h_hitem_off.reserve(ng + 1));
+            HAR_CUDA(S.pin->h_nodes.reserve(ng)); HAR_CUDA(S.pin->h_item_off.reserve(ng + 1)); HAR_CUDA(S.pin->h_res.reserve(ng)); HAR_CUDA(S.pin->h_res_stats.reserve((size_t)ng * 3 * C));
+            if (subsample) HAR_CUDA(S.pin->h_sub.reserve((size_t)ng * (K + 1) * 2));
+            HAR_CUDA(S.pin->h_hitem_off.reserve(ng + 1));
             // sibling subtraction: pair up children whose parent's counters were kept and that sit in this batch;
             // the child with fewer weighted instances (global class totals, so every rank picks the same one) is
             // accumulated from rows, the other derived.  Counter layout of the batch buffer:
             //   [accumulated nodes][class totals of all nodes][derived nodes]   (memset / all-reduce cover the first two)
-            batch_stamp++;
+            S.batch_stamp++;
             int n_derived = 0;
             if (subtract) {
                 for (int g = 0; g < ng; g++) {
-                    LNode& nd = trees[group[g0 + g].tree][group[g0 + g].node];
-                    nd.batch_pos = g; nd.batch_stamp = batch_stamp;
+                    LNode& nd = trees[S.group[S.g0 + g].tree][S.group[S.g0 + g].node];
+                    nd.batch_pos = g; nd.batch_stamp = S.batch_stamp;
                 }
             }
-            auto weight_of = [&](int t, int ni) {
-                uint64_t w = 0;
-                for (int c = 0; c < C; c++) w += tree_stats[t][(size_t)ni * C + c];
-                return w;
-            };
             for (int g = 0; g < ng; g++) {                          // who is derived, who may be kept
-                NodeDesc& d = h_nodes.p[g];
+                NodeDesc& d = S.pin->h_nodes.p[g];
                 d.sib = -1; d.from = nullptr; d.save = nullptr;
                 if (!subtract) continue;
-                const int t = group[g0 + g].tree, ni = group[g0 + g].node;
+                const int t = S.group[S.g0 + g].tree, ni = S.group[S.g0 + g].node;
                 const LNode& nd = trees[t][ni];
-                if (level_of(nd.id) + 1 < p->max_depth) {          // its children can still be split: counters may be kept
-                    HAR_CUDA(store.get(&group_slot[g0 + g], s));
-                    d.save = group_slot[g0 + g];
+                if (nd.level + 1 < p->max_depth) {                 // its children can still be split: counters may be kept
+                    HAR_CUDA(S.store.get(&S.group_slot[S.g0 + g], s));
+                    d.save = S.group_slot[S.g0 + g];
                 }
                 if (nd.parent < 0) continue;
                 const LNode& par = trees[t][nd.parent];
                 if (!par.kept) continue;
                 const LNode& sb = trees[t][par.left == ni ? par.right : par.left];
-                if (sb.batch_stamp != batch_stamp) continue;
-                const int derived_child = weight_of(t, par.left) <= weight_of(t, par.right) ? par.right : par.left;
-                if (derived_child == ni) { d.sib = sb.batch_pos; d.from = par.kept; n_derived++; }
+                if (sb.batch_stamp != S.batch_stamp) continue;
+                if (nd.derive_pref) { d.sib = sb.batch_pos; d.from = par.kept; n_derived++; }
             }
             int64_t hb = 0, items = 0, hitems = 0, hist_rows = 0;
             int64_t derived_base = (int64_t)(ng - n_derived) * full_len + (int64_t)ng * C;   // used when !subsample
             for (int g = 0; g < ng; g++) {
-                const LNode& nd = trees[group[g0 + g].tree][group[g0 + g].node];
-                NodeDesc& d = h_nodes.p[g];
-                d.start = nd.start; d.count = nd.count; d.tree = group[g0 + g].tree; d.buf = nd.buf;
-                d.level = level_of(nd.id);
+                const LNode& nd = trees[S.group[S.g0 + g].tree][S.group[S.g0 + g].node];
+                NodeDesc& d = S.pin->h_nodes.p[g];
+                d.start = nd.start; d.count = nd.count; d.tree = S.group[S.g0 + g].tree; d.buf = nd.buf;
+                d.level = nd.level;
                 if (subsample) {
                     d.sub_off = g * (K + 1); d.nf = K;
-                    int32_t* fl = h_sub.p + (size_t)g * (K + 1);
-                    int32_t* lo = h_sub.p + (size_t)ng * (K + 1) + (size_t)g * (K + 1);
+                    int32_t* fl = S.pin->h_sub.p + (size_t)g * (K + 1);
+                    int32_t* lo = S.pin->h_sub.p + (size_t)ng * (K + 1) + (size_t)g * (K + 1);
                     int32_t off = 0;
                     for (int j = 0; j < K; j++) { fl[j] = nd.subset[j]; lo[j] = off; off += m.hist_bins[nd.subset[j]] * C; }
                     fl[K] = 0; lo[K] = off;
@@ -765,120 +831,139 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 } else { d.sub_off = 0; d.nf = F; d.hist_len = (int32_t)full_len; }
                 if (d.sib < 0) { d.hist_base = hb; hb += d.hist_len; }
                 else { d.hist_base = derived_base; derived_base += d.hist_len; }
-                h_item_off.p[g] = (int32_t)items;
+                S.pin->h_item_off.p[g] = (int32_t)items;
                 items += ceil_div(nd.count, chunk_rows);
-                h_hitem_off.p[g] = (int32_t)hitems;
+                S.pin->h_hitem_off.p[g] = (int32_t)hitems;
                 if (d.sib < 0) { hitems += ceil_div(nd.count, chunk_rows); hist_rows += nd.count; }
             }
-            h_item_off.p[ng] = (int32_t)items;
-            h_hitem_off.p[ng] = (int32_t)hitems;
+            S.pin->h_item_off.p[ng] = (int32_t)items;
+            S.pin->h_hitem_off.p[ng] = (int32_t)hitems;
             // [0, hb): accumulated counters; [hb, hb + ng*C): class totals; then the derived nodes' counters
             const size_t reduce_words = (size_t)hb + (size_t)ng * C;
             const size_t need_hist = reduce_words + (size_t)n_derived * full_len;
             if (items > 0x7fffffff) return fail(HAR_E_UNSUPPORTED, "too many work items in one batch");
             // device buffers (grow-only)
-            if ((size_t)ng > cap_nodes) {
-                cap_nodes = (size_t)ng * 2;
-                HAR_CUDA(d_nodes.alloc(cap_nodes, s)); HAR_CUDA(d_res.alloc(cap_nodes, s)); HAR_CUDA(d_item_off.alloc(cap_nodes + 1, s));
-                HAR_CUDA(d_hitem_off.alloc(cap_nodes + 1, s));
+            if ((size_t)ng > S.cap_nodes) {
+                S.cap_nodes = (size_t)ng * 2;
+                HAR_CUDA(S.d_nodes.alloc(S.cap_nodes, s)); HAR_CUDA(S.d_res.alloc(S.cap_nodes, s)); HAR_CUDA(S.d_item_off.alloc(S.cap_nodes + 1, s));
+                HAR_CUDA(S.d_res_stats.alloc(S.cap_nodes * 3 * C, s));
+                HAR_CUDA(S.d_hitem_off.alloc(S.cap_nodes + 1, s));
             }
-            if (need_hist > cap_hist) { cap_hist = need_hist + need_hist / 4; HAR_CUDA(d_hist.alloc(cap_hist, s)); }
-            if ((size_t)items + 1 > cap_items) { cap_items = (size_t)items * 2 + 1; HAR_CUDA(d_chunk_left.alloc(cap_items, s)); }
-            if (subsample && (size_t)ng * (K + 1) * 2 > cap_sub) {
-                cap_sub = (size_t)ng * (K + 1) * 4;
-                HAR_CUDA(d_flist_all.alloc(cap_sub, s));
+            if (need_hist > S.cap_hist) { S.cap_hist = need_hist + need_hist / 4; HAR_CUDA(S.d_hist.alloc(S.cap_hist, s)); }
+            if ((size_t)items + 1 > S.cap_items) { S.cap_items = (size_t)items * 2 + 1; HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, s)); }
+            if (subsample && (size_t)ng * (K + 1) * 2 > S.cap_sub) {
+                S.cap_sub = (size_t)ng * (K + 1) * 4;
+                HAR_CUDA(S.d_flist_all.alloc(S.cap_sub, s));
             }
             const int32_t* flist_p = nullptr;
             const int32_t* loff_p = d_loff_all.p;
             if (subsample) {
-                HAR_CUDA(cudaMemcpyAsync(d_flist_all.p, h_sub.p, sizeof(int32_t) * (size_t)ng * (K + 1) * 2, cudaMemcpyHostToDevice, s));
-                flist_p = d_flist_all.p;
-                loff_p = d_flist_all.p + (size_t)ng * (K + 1);
+                HAR_CUDA(cudaMemcpyAsync(S.d_flist_all.p, S.pin->h_sub.p, sizeof(int32_t) * (size_t)ng * (K + 1) * 2, cudaMemcpyHostToDevice, s));
+                flist_p = S.d_flist_all.p;
+                loff_p = S.d_flist_all.p + (size_t)ng * (K + 1);
             }
-            HAR_CUDA(cudaMemcpyAsync(d_nodes.p, h_nodes.p, sizeof(NodeDesc) * ng, cudaMemcpyHostToDevice, s));
-            HAR_CUDA(cudaMemcpyAsync(d_item_off.p, h_item_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, s));
-            HAR_CUDA(cudaMemcpyAsync(d_hitem_off.p, h_hitem_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, s));
-            HAR_CUDA(cudaMemsetAsync(d_hist.p, 0, sizeof(uint32_t) * reduce_words, s));
-            uint32_t* d_parent = d_hist.p + hb;
+            HAR_CUDA(cudaMemcpyAsync(S.d_nodes.p, S.pin->h_nodes.p, sizeof(NodeDesc) * ng, cudaMemcpyHostToDevice, s));
+            HAR_CUDA(cudaMemcpyAsync(S.d_item_off.p, S.pin->h_item_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, s));
+            HAR_CUDA(cudaMemcpyAsync(S.d_hitem_off.p, S.pin->h_hitem_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, s));
+            HAR_CUDA(cudaMemsetAsync(S.d_hist.p, 0, sizeof(uint32_t) * reduce_words, s));
+            uint32_t* d_parent = S.d_hist.p + hb;
             if (hitems > 0) {
                 prof_begin(s);
                 if (subsample)
-                    k_node_hist<true><<<(unsigned)hitems, HIST_THREADS, hist_smem, s>>>(d_nodes.p, d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
-                        d_lab.p, d_w, n, perm0.p, perm1.p, flist_p, loff_p, d_kind.p, C, d_hist.p, d_parent);
+                    k_node_hist<true><<<(unsigned)hitems, HIST_THREADS, hist_smem, s>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
+                        d_lab.p, d_w, n, perm0.p, perm1.p, flist_p, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
                 else
-                    k_node_hist<false><<<(unsigned)hitems, HIST_THREADS, hist_smem, s>>>(d_nodes.p, d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
-                        d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, d_hist.p, d_parent);
+                    k_node_hist<false><<<(unsigned)hitems, HIST_THREADS, hist_smem, s>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
+                        d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
                 HAR_LAUNCH_CHECK();
                 prof_end(PROF_NODE_HIST, s, (double)hist_rows);
             }
             // the only exchange on the path: reduceByKey(_.merge(_)) -> all-reduce of the batch's counters
-            if (int rc = dist_allreduce(dist, d_hist.p, (int64_t)reduce_words, s)) return rc;
+            if (int rc = dist_allreduce(dist, S.d_hist.p, (int64_t)reduce_words, s)) return rc;
             const unsigned copy_slices = (unsigned)std::max<int64_t>(1, std::min<int64_t>(8, full_len / 2048));
             if (n_derived > 0) {
-                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, s>>>(d_nodes.p, C, d_hist.p, d_parent);
+                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, s>>>(S.d_nodes.p, C, S.d_hist.p, d_parent);
                 HAR_LAUNCH_CHECK();
             }
             prof_begin(s);
-            k_best_split<<<ng, BS_THREADS, bs_smem, s>>>(d_nodes.p, ng, d_hist.p, d_parent, flist_p, loff_p, subsample ? 1 : 0, fm, d_res.p);
+            k_best_split<<<ng, BS_THREADS, bs_smem, s>>>(S.d_nodes.p, ng, S.d_hist.p, d_parent, flist_p, loff_p, subsample ? 1 : 0, fm, S.d_res.p, S.d_res_stats.p);
             HAR_LAUNCH_CHECK();
             prof_end(PROF_BEST_SPLIT, s, (double)ng);
             if (subtract && !all_last_level) {
-                k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, s>>>(d_nodes.p, d_res.p, C, d_hist.p, d_parent);
+                k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, s>>>(S.d_nodes.p, S.d_res.p, C, S.d_hist.p, d_parent);
                 HAR_LAUNCH_CHECK();
             }
             if (!all_last_level && items > 0) {
                 prof_begin(s);
-                k_part_count<<<(unsigned)items, HIST_THREADS, 0, s>>>(d_nodes.p, d_item_off.p, ng, chunk_rows, d_res.p, d_bins.p, ldb, n,
-                                                                      perm0.p, perm1.p, d_chunk_left.p);
+                k_part_count<<<(unsigned)items, HIST_THREADS, 0, s>>>(S.d_nodes.p, S.d_item_off.p, ng, chunk_rows, S.d_res.p, d_bins.p, ldb, n,
+                                                                      perm0.p, perm1.p, S.d_chunk_left.p);
                 HAR_LAUNCH_CHECK();
                 prof_end(PROF_PART_COUNT, s, (double)rows_total);
-                k_part_scan<<<(unsigned)ceil_div(ng, 4), 128, 0, s>>>(d_item_off.p, ng, d_res.p, d_chunk_left.p);
+                k_part_scan<<<(unsigned)ceil_div(ng, 4), 128, 0, s>>>(S.d_item_off.p, ng, S.d_res.p, S.d_chunk_left.p);
                 HAR_LAUNCH_CHECK();
                 prof_begin(s);
-                k_part_scatter<<<(unsigned)items, HIST_THREADS, 0, s>>>(d_nodes.p, d_item_off.p, ng, chunk_rows, d_res.p, d_bins.p, ldb, n,
-                                                                        perm0.p, perm1.p, d_chunk_left.p);
+                k_part_scatter<<<(unsigned)items, HIST_THREADS, 0, s>>>(S.d_nodes.p, S.d_item_off.p, ng, chunk_rows, S.d_res.p, d_bins.p, ldb, n,
+                                                                        perm0.p, perm1.p, S.d_chunk_left.p);
                 HAR_LAUNCH_CHECK();
                 prof_end(PROF_PART_SCATTER, s, (double)rows_total);
             }
-            HAR_CUDA(cudaMemcpyAsync(h_res.p, d_res.p, sizeof(NodeResult) * ng, cudaMemcpyDeviceToHost, s));
+            HAR_CUDA(cudaMemcpyAsync(S.pin->h_res.p, S.d_res.p, sizeof(NodeResult) * ng, cudaMemcpyDeviceToHost, s));
+            HAR_CUDA(cudaMemcpyAsync(S.pin->h_res_stats.p, S.d_res_stats.p, sizeof(uint32_t) * (size_t)ng * 3 * C, cudaMemcpyDeviceToHost, s));
+            HAR_CUDA(cudaEventRecord(S.ev, s));
+            S.cur_g0 = S.g0; S.cur_ng = ng; S.g0 = g1; S.inflight = true;
             t_prep += ms_since(t_a);
-            t_a = now();
-            HAR_CUDA(cudaStreamSynchronize(s));
-            t_wait += ms_since(t_a);
-            t_a = now();
-            if (ng == ng_total) res_ptr = h_res.p;                 // whole group in one batch: read the staging buffer in place
-            else {
-                if ((int64_t)group_res.size() < ng_total) group_res.resize(ng_total);
-                std::copy(h_res.p, h_res.p + ng, group_res.begin() + g0);
-                res_ptr = group_res.data();
-            }
-            g0 = g1;
         }
+        return HAR_OK;
+    };
 
-        // ---- driver side of findBestSplits: children, leaf rules, stack pushes ----
+    auto collect_batch = [&](FitSet& S) -> int {
+        auto t_a = now();
+        HAR_CUDA(cudaEventSynchronize(S.ev));
+        t_wait += ms_since(t_a);
+        t_a = now();
+        {
+            if (S.cur_ng == S.ng_total) { S.res_ptr = S.pin->h_res.p; S.stat_ptr = S.pin->h_res_stats.p; }   // whole S.group in one batch: read the staging buffers in place
+            else {
+                if ((int64_t)S.group_res.size() < S.ng_total) S.group_res.resize(S.ng_total);
+                std::copy(S.pin->h_res.p, S.pin->h_res.p + S.cur_ng, S.group_res.begin() + S.cur_g0);
+                S.res_ptr = S.group_res.data();
+                if (S.group_stats.size() < (size_t)S.ng_total * 3 * C) S.group_stats.resize((size_t)S.ng_total * 3 * C);
+                std::copy(S.pin->h_res_stats.p, S.pin->h_res_stats.p + (size_t)S.cur_ng * 3 * C, S.group_stats.begin() + (size_t)S.cur_g0 * 3 * C);
+                S.stat_ptr = S.group_stats.data();
+            }
+        }
+        S.inflight = false;
+        t_post += ms_since(t_a);
+        return HAR_OK;
+    };
+
+    auto post_group = [&](FitSet& S) {
+        auto t_a = now();
+        // ---- driver side of findBestSplits: children, leaf rules, S.stack pushes ----
         // Trees are independent, so they are processed by a few host threads; the pushes are then appended
         // in the order Spark's `nodesForGroup.foreach` would produce (Scala mutable.HashMap order of the tree
         // indices, pop order inside a tree).
         std::vector<int> tkeys;
         {
             std::vector<char> seen(T, 0);
-            for (auto& gi : group) if (!seen[gi.tree]) { seen[gi.tree] = 1; tkeys.push_back(gi.tree); }
+            for (auto& gi : S.group) if (!seen[gi.tree]) { seen[gi.tree] = 1; tkeys.push_back(gi.tree); }
         }
         std::vector<int> torder = scala_hashmap_order(tkeys);
         std::vector<std::vector<int>> by_tree(T), pushes(T);
         std::vector<std::vector<uint32_t*>> released(T);
-        for (int g = 0; g < (int)ng_total; g++) by_tree[group[g].tree].push_back(g);
+        for (int g = 0; g < (int)S.ng_total; g++) by_tree[S.group[g].tree].push_back(g);
         auto process_tree = [&](int t) {
             std::vector<LNode>& tr = trees[t];
             std::vector<uint32_t>& ts = tree_stats[t];
             tr.reserve(tr.size() + 2 * by_tree[t].size());
             ts.reserve((tr.size() + 2 * by_tree[t].size()) * C);
             for (int g : by_tree[t]) {
-                const NodeResult& r = res_ptr[g];
-                const int ni = group[g].node;
-                const int level = level_of(tr[ni].id);
+                const NodeResult& r = S.res_ptr[g];
+                const uint32_t* rs = S.stat_ptr + (size_t)g * 3 * C;
+                const int ni = S.group[g].node;
+                const int level = tr[ni].level;
                 const bool is_leaf = !(r.gain > 0.0) || level == p->max_depth;
-                uint32_t* slot = subtract ? group_slot[g] : nullptr;
+                uint32_t* slot = subtract ? S.group_slot[g] : nullptr;
                 {
                     LNode& nd = tr[ni];
                     if (nd.parent >= 0) {                           // this child is done: drop the parent's kept counters after both
@@ -886,7 +971,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                         if (par.kept && --par.kids_pending == 0) { released[t].push_back(par.kept); par.kept = nullptr; }
                     }
                     nd.is_leaf = is_leaf; nd.valid = r.valid != 0; nd.gain = r.gain; nd.impurity = r.impurity;
-                    for (int c = 0; c < C; c++) ts[(size_t)ni * C + c] = r.parent[c];
+                    for (int c = 0; c < C; c++) ts[(size_t)ni * C + c] = rs[2 * C + c];
                     if (!nd.subset.empty()) std::vector<int32_t>().swap(nd.subset);
                 }
                 if (is_leaf) { if (slot) released[t].push_back(slot); continue; }
@@ -899,30 +984,60 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 LNode& L = tr[li]; LNode& R = tr[li + 1];
                 L.id = nd.id * 2; R.id = L.id + 1;
                 L.parent = R.parent = ni;
+                L.level = R.level = level + 1;
+                {   // global class totals, so every rank derives the same child
+                    uint64_t wl = 0, wr = 0;
+                    for (int c = 0; c < C; c++) { wl += rs[c]; wr += rs[C + c]; }
+                    R.derive_pref = wl <= wr; L.derive_pref = !R.derive_pref;
+                }
                 if (slot) {
                     if (r.retain) { nd.kept = slot; nd.kids_pending = 2; }
                     else released[t].push_back(slot);
                 }
                 L.is_leaf = ll; R.is_leaf = rl; L.impurity = r.left_imp; R.impurity = r.right_imp;
                 ts.resize((size_t)(li + 2) * C);
-                for (int c = 0; c < C; c++) { ts[(size_t)li * C + c] = r.left[c]; ts[(size_t)(li + 1) * C + c] = r.right[c]; }
+                for (int c = 0; c < C; c++) { ts[(size_t)li * C + c] = rs[c]; ts[(size_t)(li + 1) * C + c] = rs[C + c]; }
                 L.start = nd.start; L.count = parted ? r.n_left : 0; L.buf = nd.buf ^ 1;
                 R.start = nd.start + L.count; R.count = parted ? nd.count - r.n_left : 0; R.buf = nd.buf ^ 1;
                 nd.left = li; nd.right = li + 1;
                 nd.feature = r.feature; nd.kind = r.kind; nd.split = r.split; nd.mask = r.left_mask; nd.arity = m.arity[r.feature];
                 nd.threshold = r.kind == KIND_CONT ? fo->thresholds[(size_t)r.feature * MB + r.split] : 0.0;
+                L.pushed = !ll; R.pushed = !rl;
                 if (!ll) pushes[t].push_back(li);
                 if (!rl) pushes[t].push_back(li + 1);
             }
         };
-        parallel_for((int)tkeys.size(), ng_total >= 512, [&](int k) { process_tree(tkeys[k]); });
+        parallel_for((int)tkeys.size(), S.ng_total >= 512, [&](int k) { process_tree(tkeys[k]); });
         for (int oi : torder) {
             const int t = tkeys[oi];
-            for (int ni : pushes[t]) stack.push_back({t, ni});
-            for (uint32_t* sl : released[t]) store.put(sl);
+            for (int ni : pushes[t]) S.stack.push_back({t, ni});
+            for (uint32_t* sl : released[t]) S.store.put(sl);
         }
         t_post += ms_since(t_a);
+    };
+
+    // one step of a set: finish its batch in flight, then enqueue the next one (of this group, or of the next group)
+    auto advance = [&](FitSet& S) -> int {
+        if (S.inflight) { if (int rc = collect_batch(S)) return rc; }
+        if (S.g0 == S.ng_total) {
+            if (S.ng_total > 0) post_group(S);
+            if (S.stack.empty()) { S.done = true; S.ng_total = 0; S.g0 = 0; return HAR_OK; }
+            auto t_a = now();
+            select_group(S);
+            t_prep += ms_since(t_a);
+        }
+        return enqueue_batch(S);
+    };
+    for (;;) {
+        bool any = false;
+        for (int k = 0; k < num_sets; k++) {
+            if (sets[k].done) continue;
+            if (int rc = advance(sets[k])) return rc;
+            any = any || !sets[k].done;
+        }
+        if (!any) break;
     }
+    if (num_sets == 1) fo->num_groups = groups_run;
     auto t_emit = now();
 
     // ---- toNode(prune = true): per tree in parallel, then concatenated in tree order ----
@@ -967,11 +1082,17 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         });
     }
     fo->tree_off[T] = (int64_t)fo->feature.size();
+    if (num_sets > 1) {
+        // Spark's node-group count is not needed to train or predict: recount it on demand (har_forest_fit_info)
+        auto kept = std::make_shared<std::vector<std::vector<LNode>>>(std::move(trees));
+        const int64_t cost = (int64_t)C * total_bins_all * 8, max_mem = p->max_memory_bytes;
+        fo->count_groups = [kept, cost, max_mem]() { return simulate_groups(*kept, cost, max_mem); };
+    }
     fo->num_launches = launches_since_reset() - launches0;
     if (trace)
         fprintf(stderr, "[har_forest_fit] setup %.2f ms | loop: host prep+launch %.2f, gpu wait %.2f, driver-side %.2f | toNode %.2f | "
-                        "total %.2f ms, %lld groups, %lld batches, %zu nodes\n", t_setup, t_prep, t_wait, t_post, ms_since(t_emit),
-                ms_since(t_begin), (long long)fo->num_groups, (long long)fo->num_batches, fo->feature.size());
+                        "total %.2f ms, %lld groups run, %lld batches, %zu nodes\n", t_setup, t_prep, t_wait, t_post, ms_since(t_emit),
+                ms_since(t_begin), (long long)groups_run, (long long)fo->num_batches, fo->feature.size());
     (void)world;
     *out = fo.release();
     return HAR_OK;
@@ -1014,7 +1135,11 @@ HAR_API int har_forest_fit_info(const har_forest_t* f, double* thresholds, int32
         return fail(HAR_E_INVALID, "har_forest_fit_info: forest was not fitted with max_bins = %d", max_bins);
     if (thresholds) std::copy(f->thresholds.begin(), f->thresholds.end(), thresholds);
     if (nsplits) std::copy(f->nsplits.begin(), f->nsplits.end(), nsplits);
-    if (num_groups) *num_groups = f->num_groups;
+    if (num_groups) {
+        std::lock_guard<std::mutex> lk(f->count_mu);
+        if (f->count_groups) { f->num_groups = f->count_groups(); f->count_groups = nullptr; }
+        *num_groups = f->num_groups;
+    }
     if (num_batches) *num_batches = f->num_batches;
     if (num_kernel_launches) *num_kernel_launches = f->num_launches;
     return HAR_OK;

@@ -228,8 +228,7 @@ class Forest:
         N.check(N.lib().har_forest_shape(self._h, C.byref(T), C.byref(Cn), C.byref(F), C.byref(tot)))
         self.T, self.C, self.F, self.total_nodes = T.value, Cn.value, F.value, tot.value
         self._arrays = None          # flat node arrays are copied out of the handle on first use
-        self.thresholds = self.nsplits = None
-        self.num_groups = self.num_batches = self.num_launches = 0
+        self._max_bins = None        # set by fit_forest: the fit by-products below are then read on first use
 
     def _export(self):
         n = self.total_nodes
@@ -240,12 +239,26 @@ class Forest:
         N.check(N.lib().har_forest_export(self._h, *[hptr(a[k]) for k in self.FIELDS]))
         self._arrays = a
 
+    INFO = ("thresholds", "nsplits", "num_batches", "num_launches")
+
     def __getattr__(self, name):
-        # only reached for attributes not set in __init__: the lazily exported node arrays
+        # only reached for attributes not set in __init__: the lazily exported node arrays and fit by-products
         if name in Forest.FIELDS:
             if self.__dict__.get("_arrays") is None:
                 self._export()
             return self.__dict__["_arrays"][name]
+        if name in Forest.INFO or name == "num_groups":
+            mb = self.__dict__.get("_max_bins")
+            if mb is None:                                # imported forest: nothing was fitted
+                return None if name in ("thresholds", "nsplits") else 0
+            if name == "num_groups":
+                # Spark's node-group count; the library recounts it from the trees when the fit used its own order
+                g = C.c_int64()
+                N.check(N.lib().har_forest_fit_info(self._h, None, None, mb, C.byref(g), None, None))
+                self.num_groups = g.value
+                return g.value
+            self._load_fit_info(mb)
+            return self.__dict__[name]
         raise AttributeError(name)
 
     @classmethod
@@ -261,10 +274,10 @@ class Forest:
 
     def _load_fit_info(self, max_bins):
         self.thresholds = np.zeros((self.F, max_bins)); self.nsplits = np.zeros(self.F, np.int32)
-        g, b, l = C.c_int64(), C.c_int64(), C.c_int64()
+        b, l = C.c_int64(), C.c_int64()
         N.check(N.lib().har_forest_fit_info(self._h, hptr(self.thresholds), hptr(self.nsplits), max_bins,
-                                            C.byref(g), C.byref(b), C.byref(l)))
-        self.num_groups, self.num_batches, self.num_launches = g.value, b.value, l.value
+                                            None, C.byref(b), C.byref(l)))
+        self.num_batches, self.num_launches = b.value, l.value
 
     def tree_num_nodes(self, t):
         return int(self.tree_off[t + 1] - self.tree_off[t])
@@ -330,7 +343,7 @@ def fit_forest(X, y, arity=None, num_classes=None, num_trees=1, max_depth=5, max
     N.check(N.lib().har_forest_fit(ptr(Xd), n, F, ld, ptr(yd), hptr(ar), hptr(po), len(po) - 1, C.byref(p),
                                    None if dist is None else C.byref(dist.struct), ptr(w), stream(), C.byref(h)))
     fo = Forest(h.value)
-    fo._load_fit_info(max_bins)
+    fo._max_bins = max_bins
     return fo
 
 

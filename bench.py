@@ -247,7 +247,7 @@ def run_ours(args):
         raw, prob, pred = forest.predict(feats, is_forest=True)
         ev[3].record()
         if record is not None:
-            record.append((ev, nw, forest.total_nodes, forest.num_groups, forest.num_batches,
+            record.append((ev, nw, forest.total_nodes, forest, forest.num_batches,
                            (dist.calls, dist.bytes) if dist else (0, 0)))
         return forest, pred, labels
 
@@ -406,7 +406,7 @@ def run_ours(args):
             "data": "synthetic", "config": workload_config(args, world),
             "stages": {"window_features_samples_per_s": n / (win_ms * 1e-3), "window_ms": win_ms, "rf_fit_s": stage["fit_ms"] * 1e-3,
                        "predict_ms": stage["predict_ms"], "windows_per_gpu": nw, "forest_nodes": rec[-1][2],
-                       "node_groups": rec[-1][3], "device_batches": rec[-1][4], "allreduce_calls": rec[-1][5][0],
+                       "node_groups": rec[-1][3].num_groups, "device_batches": rec[-1][4], "allreduce_calls": rec[-1][5][0],
                        "allreduce_bytes": rec[-1][5][1], "train_accuracy": train_acc},
             "roofline": roofline, "window_stage_roofline": window_roof, "kernels": roofs,
             "step_ms": [marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps)],
