@@ -2,6 +2,11 @@
 #include "har_common.cuh"
 
 #include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <memory>
+#include <mutex>
+#include <thread>
 
 namespace har {
 
@@ -58,6 +63,75 @@ HAR_API int har_stream_synchronize(har_stream_t stream) {
     HAR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return HAR_OK;
 }
+
+// ---- persistent host thread pool behind parallel_for ---------------------------------------------------
+namespace har {
+namespace {
+struct PoolJob {
+    std::function<void(int)> fn;
+    int n = 0;
+    std::atomic<int> next{0}, done{0};
+};
+struct HostPool {
+    std::mutex mu;
+    std::condition_variable cv;
+    std::vector<std::thread> workers;
+    std::shared_ptr<PoolJob> current;
+    long long gen = 0;
+    int want = 0;                  // workers 0..want-1 join the current job
+    bool stop = false;
+    ~HostPool() {
+        { std::lock_guard<std::mutex> lk(mu); stop = true; }
+        cv.notify_all();
+        for (auto& t : workers) t.join();
+    }
+    void worker(int id) {
+        long long seen = 0;
+        for (;;) {
+            std::shared_ptr<PoolJob> job;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return stop || (gen != seen && id < want); });
+                if (stop) return;
+                seen = gen;
+                job = current;
+            }
+            if (!job) continue;
+            for (int i; (i = job->next.fetch_add(1)) < job->n;) { job->fn(i); job->done.fetch_add(1); }
+        }
+    }
+    void run(int n, int threads, const std::function<void(int)>& fn) {
+        auto job = std::make_shared<PoolJob>();
+        job->fn = fn; job->n = n;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            while ((int)workers.size() < threads - 1) { int id = (int)workers.size(); workers.emplace_back([this, id] { worker(id); }); }
+            current = job; gen++; want = threads - 1;
+        }
+        cv.notify_all();
+        for (int i; (i = job->next.fetch_add(1)) < n;) { fn(i); job->done.fetch_add(1); }
+        while (job->done.load() < n) std::this_thread::yield();
+    }
+};
+HostPool& pool() { static HostPool* p = new HostPool(); return *p; }     // leaked on purpose: no join at process exit
+std::atomic<int> g_ranks_on_host{1};
+}  // namespace
+
+int host_threads() {
+    unsigned hw = std::thread::hardware_concurrency();
+    int nt = (int)std::min<unsigned>(hw ? hw : 1, 8);
+    const int ranks = std::max(1, g_ranks_on_host.load());
+    if (hw) nt = std::min(nt, std::max(1, (int)hw / ranks));
+    return nt;
+}
+void host_threads_set_ranks(int ranks_on_host) { g_ranks_on_host = std::max(1, ranks_on_host); }
+void host_pool_run(int n, const std::function<void(int)>& fn) {
+    static std::mutex one_job;                   // one fork-join at a time; nested or concurrent callers run inline
+    std::unique_lock<std::mutex> lk(one_job, std::try_to_lock);
+    if (!lk.owns_lock()) { for (int i = 0; i < n; i++) fn(i); return; }
+    pool().run(n, std::min(host_threads(), n), fn);
+}
+}  // namespace har
 
 // Kernel-launch counter for bench.py's "gpu_launches" (not part of the reference-facing surface).
 HAR_API long long har_debug_launch_count(int reset) {

@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstring>
 #include <algorithm>
+#include <functional>
 #include <string>
 #include <thread>
 #include <vector>
@@ -23,6 +24,8 @@ int fail(int code, const char* fmt, ...);
 void count_launch(int n = 1);
 long long launches_since_reset();
 void reset_launches();
+// int32 sum all-reduce of a device buffer over the ranks of `d` (no-op for one rank); har_comm.cu
+int dist_allreduce(const har_dist* d, void* buf, int64_t count, cudaStream_t s);
 
 // optional CUDA-event timing of selected kernels (har_debug_profile_*; off by default)
 enum ProfId { PROF_NODE_HIST = 0, PROF_BEST_SPLIT, PROF_PART_COUNT, PROF_PART_SCATTER, PROF_WINDOW_FEATURES,
@@ -80,20 +83,17 @@ struct DevBuf {
 
 inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
-// Small fork-join helper for the host-side (driver) work; `go` = false runs inline.
+// Fork-join helper for the host-side (driver) work; `go` = false runs inline.  The items go to a small persistent
+// pool (har_api.cu): creating threads per call cost more than the work of a node group.  The number of threads is
+// min(8, cores / ranks sharing the host) — see host_threads_set_ranks.
+void host_pool_run(int n, const std::function<void(int)>& fn);
+int host_threads();
+void host_threads_set_ranks(int ranks_on_host);
 template <typename Fn>
 void parallel_for(int n, bool go, Fn fn) {
-    unsigned hw = std::thread::hardware_concurrency();
-    int nt = (int)std::min<unsigned>(hw ? hw : 1, 8);
-    if (!go || nt <= 1 || n < 2) { for (int i = 0; i < n; i++) fn(i); return; }
-    nt = std::min(nt, n);
-    std::vector<std::thread> th;
-    th.reserve(nt);
-    for (int k = 0; k < nt; k++) th.emplace_back([=, &fn] { for (int i = k; i < n; i += nt) fn(i); });
-    for (auto& t : th) t.join();
+    if (!go || n < 2 || host_threads() <= 1) { for (int i = 0; i < n; i++) fn(i); return; }
+    host_pool_run(n, std::function<void(int)>(std::ref(fn)));
 }
-
-
 
 // java.lang.Double.compare total order as a sortable unsigned key (NaN canonical, greatest).
 __host__ __device__ inline uint64_t jd_key(double x) {

@@ -67,14 +67,6 @@ int finish_meta(Meta& m) {
     return HAR_OK;
 }
 
-int dist_allreduce(const har_dist* d, void* buf, int64_t count, cudaStream_t s) {
-    if (!d || d->world_size <= 1 || count == 0) return HAR_OK;
-    if (!d->allreduce_i32) return fail(HAR_E_INVALID, "har_dist.allreduce_i32 is NULL with world_size > 1");
-    int rc = d->allreduce_i32(d->ctx, buf, count, (har_stream_t)s);
-    if (rc != 0) return fail(HAR_E_COMM, "all-reduce callback failed with code %d", rc);
-    return HAR_OK;
-}
-
 // ---- RandomForest.findSplits row sample (RDD.sample -> BernoulliSampler / GapSampling) -----------
 void sample_rows(int64_t n_global, int mpb, int64_t seed, const int64_t* part_off, int num_parts,
                  int partition_offset, std::vector<int64_t>& out) {
@@ -534,6 +526,8 @@ HAR_API int har_node_histogram(const uint8_t* d_bins, int64_t ldb, const uint8_t
 HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, const double* d_y, const int32_t* arity,
                            const int64_t* part_off_in, int32_t num_parts, const har_fit_params* p, const har_dist* dist,
                            const uint8_t* d_weights_in, har_stream_t stream, har_forest_t** out) {
+    // host threads for the driver-side work: the ranks of a node share its cores
+    host_threads_set_ranks(dist ? dist->world_size : 1);
     if (!out || !p) return fail(HAR_E_INVALID, "har_forest_fit: NULL params / out");
     *out = nullptr;
     cudaStream_t s = (cudaStream_t)stream;
@@ -702,6 +696,10 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         std::vector<NodeResult> group_res;
         std::vector<uint32_t> group_stats;
         std::vector<uint32_t*> group_slot;                  // per node of the group: the slot its counters may be kept in
+        std::vector<int> tkeys;                             // driver-side scratch, reused across groups
+        std::vector<char> seen;
+        std::vector<std::vector<int>> by_tree, pushes;
+        std::vector<std::vector<uint32_t*>> released;
         const NodeResult* res_ptr = nullptr;
         const uint32_t* stat_ptr = nullptr;
         int64_t ng_total = 0, g0 = 0, cur_g0 = 0;
@@ -715,14 +713,21 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HistStore store;
         int64_t batch_stamp = 0;
         PinnedScratch* pin = nullptr;
+        cudaStream_t st = nullptr;                          // the set's stream (forked from the caller's)
         cudaEvent_t ev = nullptr;
         ~FitSet() { if (ev) cudaEventDestroy(ev); }
     };
     int num_sets = (!subsample && T >= 2) ? 2 : 1;
     if (const char* e = std::getenv("HAR_FIT_SETS")) num_sets = std::max(1, std::min(num_sets, std::atoi(e)));
+    // each set on its own stream: the all-reduce of one set's batch overlaps the other set's kernels
+    bool own_streams = num_sets > 1;
+    if (const char* e = std::getenv("HAR_FIT_STREAMS")) own_streams = own_streams && std::atoi(e) > 1;
+    SideStream set_side[2];
     FitSet sets[2];
     for (int k = 0; k < num_sets; k++) {
         sets[k].pin = &pinned[k];
+        sets[k].st = s;
+        if (own_streams) { HAR_CUDA(set_side[k].fork(s)); sets[k].st = set_side[k].s; }
         sets[k].store.slot_words = (size_t)full_len + C;
         HAR_CUDA(cudaEventCreateWithFlags(&sets[k].ev, cudaEventDisableTiming));
     }
@@ -803,7 +808,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 const int t = S.group[S.g0 + g].tree, ni = S.group[S.g0 + g].node;
                 const LNode& nd = trees[t][ni];
                 if (nd.level + 1 < p->max_depth) {                 // its children can still be split: counters may be kept
-                    HAR_CUDA(S.store.get(&S.group_slot[S.g0 + g], s));
+                    HAR_CUDA(S.store.get(&S.group_slot[S.g0 + g], S.st));
                     d.save = S.group_slot[S.g0 + g];
                 }
                 if (nd.parent < 0) continue;
@@ -845,71 +850,71 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             // device buffers (grow-only)
             if ((size_t)ng > S.cap_nodes) {
                 S.cap_nodes = (size_t)ng * 2;
-                HAR_CUDA(S.d_nodes.alloc(S.cap_nodes, s)); HAR_CUDA(S.d_res.alloc(S.cap_nodes, s)); HAR_CUDA(S.d_item_off.alloc(S.cap_nodes + 1, s));
-                HAR_CUDA(S.d_res_stats.alloc(S.cap_nodes * 3 * C, s));
-                HAR_CUDA(S.d_hitem_off.alloc(S.cap_nodes + 1, s));
+                HAR_CUDA(S.d_nodes.alloc(S.cap_nodes, S.st)); HAR_CUDA(S.d_res.alloc(S.cap_nodes, S.st)); HAR_CUDA(S.d_item_off.alloc(S.cap_nodes + 1, S.st));
+                HAR_CUDA(S.d_res_stats.alloc(S.cap_nodes * 3 * C, S.st));
+                HAR_CUDA(S.d_hitem_off.alloc(S.cap_nodes + 1, S.st));
             }
-            if (need_hist > S.cap_hist) { S.cap_hist = need_hist + need_hist / 4; HAR_CUDA(S.d_hist.alloc(S.cap_hist, s)); }
-            if ((size_t)items + 1 > S.cap_items) { S.cap_items = (size_t)items * 2 + 1; HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, s)); }
+            if (need_hist > S.cap_hist) { S.cap_hist = need_hist + need_hist / 4; HAR_CUDA(S.d_hist.alloc(S.cap_hist, S.st)); }
+            if ((size_t)items + 1 > S.cap_items) { S.cap_items = (size_t)items * 2 + 1; HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, S.st)); }
             if (subsample && (size_t)ng * (K + 1) * 2 > S.cap_sub) {
                 S.cap_sub = (size_t)ng * (K + 1) * 4;
-                HAR_CUDA(S.d_flist_all.alloc(S.cap_sub, s));
+                HAR_CUDA(S.d_flist_all.alloc(S.cap_sub, S.st));
             }
             const int32_t* flist_p = nullptr;
             const int32_t* loff_p = d_loff_all.p;
             if (subsample) {
-                HAR_CUDA(cudaMemcpyAsync(S.d_flist_all.p, S.pin->h_sub.p, sizeof(int32_t) * (size_t)ng * (K + 1) * 2, cudaMemcpyHostToDevice, s));
+                HAR_CUDA(cudaMemcpyAsync(S.d_flist_all.p, S.pin->h_sub.p, sizeof(int32_t) * (size_t)ng * (K + 1) * 2, cudaMemcpyHostToDevice, S.st));
                 flist_p = S.d_flist_all.p;
                 loff_p = S.d_flist_all.p + (size_t)ng * (K + 1);
             }
-            HAR_CUDA(cudaMemcpyAsync(S.d_nodes.p, S.pin->h_nodes.p, sizeof(NodeDesc) * ng, cudaMemcpyHostToDevice, s));
-            HAR_CUDA(cudaMemcpyAsync(S.d_item_off.p, S.pin->h_item_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, s));
-            HAR_CUDA(cudaMemcpyAsync(S.d_hitem_off.p, S.pin->h_hitem_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, s));
-            HAR_CUDA(cudaMemsetAsync(S.d_hist.p, 0, sizeof(uint32_t) * reduce_words, s));
+            HAR_CUDA(cudaMemcpyAsync(S.d_nodes.p, S.pin->h_nodes.p, sizeof(NodeDesc) * ng, cudaMemcpyHostToDevice, S.st));
+            HAR_CUDA(cudaMemcpyAsync(S.d_item_off.p, S.pin->h_item_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, S.st));
+            HAR_CUDA(cudaMemcpyAsync(S.d_hitem_off.p, S.pin->h_hitem_off.p, sizeof(int32_t) * (ng + 1), cudaMemcpyHostToDevice, S.st));
+            HAR_CUDA(cudaMemsetAsync(S.d_hist.p, 0, sizeof(uint32_t) * reduce_words, S.st));
             uint32_t* d_parent = S.d_hist.p + hb;
             if (hitems > 0) {
-                prof_begin(s);
+                prof_begin(S.st);
                 if (subsample)
-                    k_node_hist<true><<<(unsigned)hitems, HIST_THREADS, hist_smem, s>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
+                    k_node_hist<true><<<(unsigned)hitems, HIST_THREADS, hist_smem, S.st>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
                         d_lab.p, d_w, n, perm0.p, perm1.p, flist_p, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
                 else
-                    k_node_hist<false><<<(unsigned)hitems, HIST_THREADS, hist_smem, s>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
+                    k_node_hist<false><<<(unsigned)hitems, HIST_THREADS, hist_smem, S.st>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
                         d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
                 HAR_LAUNCH_CHECK();
-                prof_end(PROF_NODE_HIST, s, (double)hist_rows);
+                prof_end(PROF_NODE_HIST, S.st, (double)hist_rows);
             }
             // the only exchange on the path: reduceByKey(_.merge(_)) -> all-reduce of the batch's counters
-            if (int rc = dist_allreduce(dist, S.d_hist.p, (int64_t)reduce_words, s)) return rc;
+            if (int rc = dist_allreduce(dist, S.d_hist.p, (int64_t)reduce_words, S.st)) return rc;
             const unsigned copy_slices = (unsigned)std::max<int64_t>(1, std::min<int64_t>(8, full_len / 2048));
             if (n_derived > 0) {
-                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, s>>>(S.d_nodes.p, C, S.d_hist.p, d_parent);
+                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(S.d_nodes.p, C, S.d_hist.p, d_parent);
                 HAR_LAUNCH_CHECK();
             }
-            prof_begin(s);
-            k_best_split<<<ng, BS_THREADS, bs_smem, s>>>(S.d_nodes.p, ng, S.d_hist.p, d_parent, flist_p, loff_p, subsample ? 1 : 0, fm, S.d_res.p, S.d_res_stats.p);
+            prof_begin(S.st);
+            k_best_split<<<ng, BS_THREADS, bs_smem, S.st>>>(S.d_nodes.p, ng, S.d_hist.p, d_parent, flist_p, loff_p, subsample ? 1 : 0, fm, S.d_res.p, S.d_res_stats.p);
             HAR_LAUNCH_CHECK();
-            prof_end(PROF_BEST_SPLIT, s, (double)ng);
+            prof_end(PROF_BEST_SPLIT, S.st, (double)ng);
             if (subtract && !all_last_level) {
-                k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, s>>>(S.d_nodes.p, S.d_res.p, C, S.d_hist.p, d_parent);
+                k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(S.d_nodes.p, S.d_res.p, C, S.d_hist.p, d_parent);
                 HAR_LAUNCH_CHECK();
             }
             if (!all_last_level && items > 0) {
-                prof_begin(s);
-                k_part_count<<<(unsigned)items, HIST_THREADS, 0, s>>>(S.d_nodes.p, S.d_item_off.p, ng, chunk_rows, S.d_res.p, d_bins.p, ldb, n,
+                prof_begin(S.st);
+                k_part_count<<<(unsigned)items, HIST_THREADS, 0, S.st>>>(S.d_nodes.p, S.d_item_off.p, ng, chunk_rows, S.d_res.p, d_bins.p, ldb, n,
                                                                       perm0.p, perm1.p, S.d_chunk_left.p);
                 HAR_LAUNCH_CHECK();
-                prof_end(PROF_PART_COUNT, s, (double)rows_total);
-                k_part_scan<<<(unsigned)ceil_div(ng, 4), 128, 0, s>>>(S.d_item_off.p, ng, S.d_res.p, S.d_chunk_left.p);
+                prof_end(PROF_PART_COUNT, S.st, (double)rows_total);
+                k_part_scan<<<(unsigned)ceil_div(ng, 4), 128, 0, S.st>>>(S.d_item_off.p, ng, S.d_res.p, S.d_chunk_left.p);
                 HAR_LAUNCH_CHECK();
-                prof_begin(s);
-                k_part_scatter<<<(unsigned)items, HIST_THREADS, 0, s>>>(S.d_nodes.p, S.d_item_off.p, ng, chunk_rows, S.d_res.p, d_bins.p, ldb, n,
+                prof_begin(S.st);
+                k_part_scatter<<<(unsigned)items, HIST_THREADS, 0, S.st>>>(S.d_nodes.p, S.d_item_off.p, ng, chunk_rows, S.d_res.p, d_bins.p, ldb, n,
                                                                         perm0.p, perm1.p, S.d_chunk_left.p);
                 HAR_LAUNCH_CHECK();
-                prof_end(PROF_PART_SCATTER, s, (double)rows_total);
+                prof_end(PROF_PART_SCATTER, S.st, (double)rows_total);
             }
-            HAR_CUDA(cudaMemcpyAsync(S.pin->h_res.p, S.d_res.p, sizeof(NodeResult) * ng, cudaMemcpyDeviceToHost, s));
-            HAR_CUDA(cudaMemcpyAsync(S.pin->h_res_stats.p, S.d_res_stats.p, sizeof(uint32_t) * (size_t)ng * 3 * C, cudaMemcpyDeviceToHost, s));
-            HAR_CUDA(cudaEventRecord(S.ev, s));
+            HAR_CUDA(cudaMemcpyAsync(S.pin->h_res.p, S.d_res.p, sizeof(NodeResult) * ng, cudaMemcpyDeviceToHost, S.st));
+            HAR_CUDA(cudaMemcpyAsync(S.pin->h_res_stats.p, S.d_res_stats.p, sizeof(uint32_t) * (size_t)ng * 3 * C, cudaMemcpyDeviceToHost, S.st));
+            HAR_CUDA(cudaEventRecord(S.ev, S.st));
             S.cur_g0 = S.g0; S.cur_ng = ng; S.g0 = g1; S.inflight = true;
             t_prep += ms_since(t_a);
         }
@@ -943,14 +948,14 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         // Trees are independent, so they are processed by a few host threads; the pushes are then appended
         // in the order Spark's `nodesForGroup.foreach` would produce (Scala mutable.HashMap order of the tree
         // indices, pop order inside a tree).
-        std::vector<int> tkeys;
-        {
-            std::vector<char> seen(T, 0);
-            for (auto& gi : S.group) if (!seen[gi.tree]) { seen[gi.tree] = 1; tkeys.push_back(gi.tree); }
-        }
+        std::vector<int>& tkeys = S.tkeys;
+        std::vector<std::vector<int>>&by_tree = S.by_tree, &pushes = S.pushes;
+        std::vector<std::vector<uint32_t*>>& released = S.released;
+        if (by_tree.empty()) { by_tree.resize(T); pushes.resize(T); released.resize(T); S.seen.assign(T, 0); }
+        tkeys.clear();
+        for (auto& gi : S.group) if (!S.seen[gi.tree]) { S.seen[gi.tree] = 1; tkeys.push_back(gi.tree); }
+        for (int t : tkeys) { S.seen[t] = 0; by_tree[t].clear(); pushes[t].clear(); released[t].clear(); }
         std::vector<int> torder = scala_hashmap_order(tkeys);
-        std::vector<std::vector<int>> by_tree(T), pushes(T);
-        std::vector<std::vector<uint32_t*>> released(T);
         for (int g = 0; g < (int)S.ng_total; g++) by_tree[S.group[g].tree].push_back(g);
         auto process_tree = [&](int t) {
             std::vector<LNode>& tr = trees[t];
@@ -1037,6 +1042,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         }
         if (!any) break;
     }
+    for (int k = 0; k < num_sets; k++) HAR_CUDA(set_side[k].join(s));
     if (num_sets == 1) fo->num_groups = groups_run;
     auto t_emit = now();
 

@@ -78,6 +78,13 @@ def parts(n, part_off):
     return po
 
 
+def comm_stats(reset=False):
+    """(all-reduce calls, bytes, 1 if the library's own NCCL communicator carries them) since the last reset."""
+    c, b, v = C.c_longlong(), C.c_longlong(), C.c_int()
+    N.lib().har_debug_comm_stats(C.byref(c), C.byref(b), C.byref(v), 1 if reset else 0)
+    return int(c.value), int(b.value), int(v.value)
+
+
 def launch_count(reset=False):
     return int(N.lib().har_debug_launch_count(1 if reset else 0))
 

@@ -48,10 +48,20 @@ class Dist:
         self.calls = 0
         self.bytes = 0
 
+        streams = {}
+
         def _cb(ctx, ptr, count, stream):
             try:
                 t = wrap_i32(ptr, count, self._device)
-                td.all_reduce(t, op=td.ReduceOp.SUM, group=self._group)
+                if self._device is not None and stream:
+                    # the library may call from a stream of its own (one per tree set): order the collective there
+                    st = streams.get(stream)
+                    if st is None:
+                        st = streams[stream] = torch.cuda.ExternalStream(stream, device=self._device)
+                    with torch.cuda.stream(st):
+                        td.all_reduce(t, op=td.ReduceOp.SUM, group=self._group)
+                else:
+                    td.all_reduce(t, op=td.ReduceOp.SUM, group=self._group)
                 self.calls += 1
                 self.bytes += 4 * count
                 return 0

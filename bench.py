@@ -241,14 +241,16 @@ def run_ours(args):
             cnt = torch.tensor([nw], dtype=torch.int64, device="cuda")
             td.all_reduce(cnt)
             dist = Dist(int(cnt.item()), rank * P, world * P)
+        core.comm_stats(reset=True)
         forest = core.fit_forest(feats, labels, num_classes=6, num_trees=args.trees, max_depth=args.depth, max_bins=32,
                                  feature_subset="all", seed=2018, part_off=po, dist=dist)
+        comm = core.comm_stats()
         ev[2].record()
         raw, prob, pred = forest.predict(feats, is_forest=True)
         ev[3].record()
         if record is not None:
             record.append((ev, nw, forest.total_nodes, forest, forest.num_batches,
-                           (dist.calls, dist.bytes) if dist else (0, 0)))
+                           comm))
         return forest, pred, labels
 
     def barrier():
@@ -406,7 +408,7 @@ def run_ours(args):
             "data": "synthetic", "config": workload_config(args, world),
             "stages": {"window_features_samples_per_s": n / (win_ms * 1e-3), "window_ms": win_ms, "rf_fit_s": stage["fit_ms"] * 1e-3,
                        "predict_ms": stage["predict_ms"], "windows_per_gpu": nw, "forest_nodes": rec[-1][2],
-                       "node_groups": rec[-1][3].num_groups, "device_batches": rec[-1][4], "allreduce_calls": rec[-1][5][0],
+                       "node_groups": rec[-1][3].num_groups, "device_batches": rec[-1][4], "allreduce_calls": rec[-1][5][0], "allreduce_via": "library NCCL communicator" if rec[-1][5][2] else "caller's callback (torch.distributed)",
                        "allreduce_bytes": rec[-1][5][1], "train_accuracy": train_acc},
             "roofline": roofline, "window_stage_roofline": window_roof, "kernels": roofs,
             "step_ms": [marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps)],

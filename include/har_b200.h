@@ -132,6 +132,11 @@ typedef struct har_fit_params {
  * ordered on `stream`.  Replaces `partitionAggregates.reduceByKey((a, b) => a.merge(b))` in
  * RandomForest.findBestSplits.  Return 0 on success. */
 typedef int (*har_allreduce_i32_fn)(void* ctx, void* d_buf, int64_t count, har_stream_t stream);
+/* With world_size > 1 the callback always carries the small exchanges (row counts, the findSplits sample).  For the
+ * per-batch counters the library prefers a communicator of its own: if libnccl.so.2 is already loaded in the
+ * process it creates one over the same ranks (the unique id is exchanged once through this callback) and calls
+ * ncclAllReduce on its own streams; HAR_NCCL=0 in the environment, or no NCCL in the process, keeps everything
+ * on the callback.  The callback must honour `stream` (the library may use streams of its own). */
 
 typedef struct har_dist {
     int32_t rank, world_size;

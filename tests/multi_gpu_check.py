@@ -56,7 +56,9 @@ for kw in (dict(num_trees=20, max_depth=8, feature_subset="all"), dict(num_trees
         for k in core.Forest.FIELDS:
             a, b = np.asarray(getattr(ref, k)), np.asarray(getattr(fo, k))
             assert a.shape == b.shape and np.array_equal(a.view(np.uint8), b.view(np.uint8)), "field %s differs between 1 and %d GPUs" % (k, world)
-        print("ok: %s -> %d nodes, %d all-reduce calls, %.1f MB reduced; identical on %d ranks and to the 1-GPU forest"
-              % (kw, fo.total_nodes, dist.calls, dist.bytes / 1e6, world))
+        calls, nbytes, via = core.comm_stats()
+        print("ok: %s -> %d nodes, %d all-reduce calls so far (%d through the callback), %.1f MB reduced, %s; identical on %d "
+              "ranks and to the 1-GPU forest" % (kw, fo.total_nodes, calls, dist.calls, nbytes / 1e6,
+                                                 "library NCCL communicator" if via else "callback only", world))
     td.barrier()
 td.destroy_process_group()
