@@ -498,7 +498,7 @@ HAR_API int har_node_histogram(const uint8_t* d_bins, int64_t ldb, const uint8_t
     const int chunk_rows = 2048;
     NodeDesc nd{};
     nd.start = 0; nd.hist_base = 0; nd.count = (int32_t)nrows; nd.tree = 0; nd.buf = 0; nd.level = 0; nd.sub_off = 0; nd.sib = -1;
-    nd.nf = F; nd.hist_len = loff[F];
+    nd.nf = F; nd.hist_len = loff[F]; nd.id = 1;
     int32_t item_off[2] = {0, (int32_t)ceil_div(nrows, chunk_rows)};
     DevBuf<NodeDesc> d_nd; DevBuf<int32_t> d_io, d_loff; DevBuf<uint8_t> d_kind;
     HAR_CUDA(d_nd.alloc(1, s)); HAR_CUDA(d_io.alloc(2, s)); HAR_CUDA(d_loff.alloc(F + 1, s)); HAR_CUDA(d_kind.alloc(F, s));
@@ -688,6 +688,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     struct PinnedScratch {
         Pinned<NodeDesc> h_nodes; Pinned<NodeResult> h_res; Pinned<uint32_t> h_res_stats;
         Pinned<int32_t> h_item_off, h_hitem_off, h_sub;
+        Pinned<BatchInfo> h_binfo; Pinned<int32_t> h_n;
+        Pinned<PoolMeta> h_meta;
     };
     // page-locked staging, kept across fits (cudaMallocHost is far too slow to repeat per call)
     static thread_local PinnedScratch pinned[2];
@@ -712,6 +714,19 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         size_t cap_nodes = 0, cap_hist = 0, cap_items = 0, cap_sub = 0;
         HistStore store;
         int64_t batch_stamp = 0;
+        // device-driven growth (all-features fits): node tables of two consecutive levels, per-batch launch data,
+        // the pool of finished nodes and the kept counters of two consecutive levels
+        std::vector<int> my_trees;
+        DevBuf<NodeDesc> lv_nodes[2];
+        DevBuf<int32_t> lv_item_off[2], lv_hitem_off[2], d_cnt, d_total;      // d_total: [children in total, copy for the host]
+        DevBuf<BatchInfo> d_binfo;
+        size_t cap_lv[2] = {0, 0}, cap_cnt = 0, cap_binfo = 0;
+        DevBuf<NodeResult> pool_res;
+        DevBuf<uint32_t> pool_stats, kept[2];
+        DevBuf<PoolMeta> pool_meta;
+        size_t cap_pool = 0, cap_kept[2] = {0, 0};
+        int64_t pool_used = 0, kept_slots[2] = {0, 0};
+        int level = 0, ncur = 0, cur = 0;
         PinnedScratch* pin = nullptr;
         cudaStream_t st = nullptr;                          // the set's stream (forked from the caller's)
         cudaEvent_t ev = nullptr;
@@ -722,11 +737,56 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     // each set on its own stream: the all-reduce of one set's batch overlaps the other set's kernels
     bool own_streams = num_sets > 1;
     if (const char* e = std::getenv("HAR_FIT_STREAMS")) own_streams = own_streams && std::atoi(e) > 1;
+    // device-driven growth (all features per node), see further down
+    bool device_grow = !subsample;
+    if (const char* e = std::getenv("HAR_FIT_DEVICE_GROW")) device_grow = device_grow && std::atoi(e) != 0;
+    const int64_t slot_words = (int64_t)full_len + C;
+    int batch_cap = (int)std::min<int64_t>(1 << 20, std::max<int64_t>(2, budget_words / std::max<int64_t>(1, slot_words)));
+    batch_cap &= ~1;                                                    // sibling pairs never straddle by parity alone
+    int64_t kept_cap_slots = (int64_t)((2LL << 30) / (slot_words * 4)); // <= 2 GB of kept counters per level buffer
+    if (const char* e = std::getenv("HAR_KEPT_SLOTS")) kept_cap_slots = std::max<int64_t>(0, std::atoll(e));   // tests
     SideStream set_side[2];
     FitSet sets[2];
     for (int k = 0; k < num_sets; k++) {
         sets[k].pin = &pinned[k];
         sets[k].st = s;
+        if (device_grow) {
+            // Everything the level loop needs is sized from bounds and allocated here, on the caller's stream, before
+            // the set streams fork: growing a buffer inside the loop makes the stream-ordered allocator reuse memory
+            // across the two set streams, which serialises them (measured: 40 ms of host time per fit).
+            FitSet& S = sets[k];
+            for (int t = k; t < T; t += num_sets) S.my_trees.push_back(t);
+            const int64_t Ts = std::max<int64_t>(1, (int64_t)S.my_trees.size());
+            const int64_t rows_g = std::max<int64_t>(1, (dist && dist->world_size > 1) ? dist->global_rows : n);
+            int64_t lvl = std::min<int64_t>(Ts << std::min(p->max_depth, 22), rows_g * Ts);
+            lvl = std::max<int64_t>(Ts, std::min<int64_t>(lvl, 4 << 20));
+            const int64_t nbl = ceil_div(lvl, batch_cap) + 2;
+            for (int w = 0; w < 2; w++) {
+                S.cap_lv[w] = (size_t)lvl;
+                HAR_CUDA(S.lv_nodes[w].alloc(lvl, s));
+                HAR_CUDA(S.lv_item_off[w].alloc(lvl + nbl + 1, s));
+                HAR_CUDA(S.lv_hitem_off[w].alloc(lvl + nbl + 1, s));
+            }
+            S.cap_binfo = (size_t)nbl;
+            HAR_CUDA(S.d_binfo.alloc(nbl, s)); HAR_CUDA(S.pin->h_binfo.reserve(nbl)); HAR_CUDA(S.pin->h_n.reserve(2));
+            S.cap_cnt = (size_t)lvl;
+            HAR_CUDA(S.d_cnt.alloc(lvl, s)); HAR_CUDA(S.d_total.alloc(2, s));
+            const int64_t per_batch = std::min<int64_t>(batch_cap, lvl);
+            S.cap_hist = (size_t)(per_batch * slot_words);
+            HAR_CUDA(S.d_hist.alloc(S.cap_hist, s));
+            S.cap_items = (size_t)(ceil_div(n * Ts, 256) + per_batch + 1);
+            HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, s));
+            int64_t kslots = 0;
+            if (subtract && p->max_depth >= 2) kslots = std::min(kept_cap_slots, std::min(lvl, Ts << std::min(p->max_depth - 2, 22)));
+            for (int w = 0; w < 2; w++) {
+                S.cap_kept[w] = (size_t)kslots;
+                if (kslots > 0) HAR_CUDA(S.kept[w].alloc((size_t)kslots * (size_t)slot_words, s));
+            }
+            int64_t pool = std::min<int64_t>(Ts << std::min(p->max_depth + 1, 23), 2 * rows_g * Ts);
+            pool = std::max<int64_t>(Ts, std::min<int64_t>(pool, 4 << 20));
+            S.cap_pool = (size_t)pool;
+            HAR_CUDA(S.pool_res.alloc(pool, s)); HAR_CUDA(S.pool_stats.alloc((size_t)pool * 3 * C, s)); HAR_CUDA(S.pool_meta.alloc(pool, s));
+        }
         if (own_streams) { HAR_CUDA(set_side[k].fork(s)); sets[k].st = set_side[k].s; }
         sets[k].store.slot_words = (size_t)full_len + C;
         HAR_CUDA(cudaEventCreateWithFlags(&sets[k].ev, cudaEventDisableTiming));
@@ -824,7 +884,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 const LNode& nd = trees[S.group[S.g0 + g].tree][S.group[S.g0 + g].node];
                 NodeDesc& d = S.pin->h_nodes.p[g];
                 d.start = nd.start; d.count = nd.count; d.tree = S.group[S.g0 + g].tree; d.buf = nd.buf;
-                d.level = nd.level;
+                d.level = nd.level; d.id = nd.id; d.pad = 0;
                 if (subsample) {
                     d.sub_off = g * (K + 1); d.nf = K;
                     int32_t* fl = S.pin->h_sub.p + (size_t)g * (K + 1);
@@ -1033,6 +1093,251 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         }
         return enqueue_batch(S);
     };
+
+    // ---- device-driven growth (all features per node) ------------------------------------------------------
+    // The host enqueues a whole level of a set at a time (its device batches, then the kernels that build the next
+    // level's node table) and reads back only the per-batch launch data; see k_grow_* in har_tree_kernels.cuh.
+
+    auto dd_ensure_level = [&](FitSet& S, int which, int64_t nodes_cap) -> int {
+        const int64_t nb = ceil_div(std::max<int64_t>(nodes_cap, 1), batch_cap);
+        if ((size_t)nodes_cap > S.cap_lv[which]) {
+            S.cap_lv[which] = (size_t)nodes_cap * 2;
+            const int64_t nb2 = ceil_div((int64_t)S.cap_lv[which], batch_cap);
+            HAR_CUDA(S.lv_nodes[which].alloc(S.cap_lv[which], S.st));
+            HAR_CUDA(S.lv_item_off[which].alloc(S.cap_lv[which] + nb2 + 1, S.st));
+            HAR_CUDA(S.lv_hitem_off[which].alloc(S.cap_lv[which] + nb2 + 1, S.st));
+        }
+        if ((size_t)nb > S.cap_binfo) {
+            S.cap_binfo = (size_t)nb * 2;
+            HAR_CUDA(S.d_binfo.alloc(S.cap_binfo, S.st));
+            HAR_CUDA(S.pin->h_binfo.reserve(S.cap_binfo));
+        }
+        return HAR_OK;
+    };
+    auto dd_ensure_kept = [&](FitSet& S, int which, int level_of_nodes, int64_t nodes_upper) -> int {
+        // nodes past the preallocated slots simply do not keep their counters (their children are accumulated from rows)
+        const int64_t slots = (subtract && level_of_nodes + 1 < p->max_depth) ? std::min<int64_t>(nodes_upper, (int64_t)S.cap_kept[which]) : 0;
+        S.kept_slots[which] = slots;
+        return HAR_OK;
+    };
+    // launch data of level `S.level` (already laid out on the device) -> host, behind an event
+    auto dd_fetch_info = [&](FitSet& S, int64_t nb_upper) -> int {
+        HAR_CUDA(S.pin->h_n.reserve(2));
+        HAR_CUDA(cudaMemcpyAsync(S.pin->h_binfo.p, S.d_binfo.p, sizeof(BatchInfo) * nb_upper, cudaMemcpyDeviceToHost, S.st));
+        HAR_CUDA(cudaMemcpyAsync(S.pin->h_n.p, S.d_total.p + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, S.st));
+        HAR_CUDA(cudaEventRecord(S.ev, S.st));
+        S.inflight = true;
+        return HAR_OK;
+    };
+    auto dd_start = [&](FitSet& S) -> int {
+        auto t_a = now();
+        const int nr = (int)S.my_trees.size();
+        S.level = 0; S.cur = 0; S.ncur = nr;
+        if (nr == 0) { S.done = true; return HAR_OK; }
+        if (int rc = dd_ensure_level(S, 0, nr)) return rc;
+        if (int rc = dd_ensure_kept(S, 0, 0, nr)) return rc;
+        HAR_CUDA(S.pin->h_nodes.reserve(nr));
+        for (int q = 0; q < nr; q++) {
+            NodeDesc& d = S.pin->h_nodes.p[q];
+            const int t = S.my_trees[q];
+            d.start = 0; d.hist_base = 0; d.count = root_cnt[t]; d.tree = t; d.buf = 0; d.level = 0;
+            d.sub_off = 0; d.nf = F; d.hist_len = (int32_t)full_len; d.sib = -1; d.from = nullptr;
+            d.save = q < S.kept_slots[0] ? S.kept[0].p + (int64_t)q * slot_words : nullptr;
+            d.id = 1; d.pad = 0;
+        }
+        HAR_CUDA(cudaMemcpyAsync(S.lv_nodes[0].p, S.pin->h_nodes.p, sizeof(NodeDesc) * nr, cudaMemcpyHostToDevice, S.st));
+        HAR_CUDA(S.pin->h_n.reserve(2));
+        S.pin->h_n.p[1] = nr;
+        HAR_CUDA(cudaMemcpyAsync(S.d_total.p, S.pin->h_n.p + 1, sizeof(int32_t), cudaMemcpyHostToDevice, S.st));
+        const int64_t nb = ceil_div(nr, batch_cap);
+        k_grow_layout<<<(unsigned)nb, 256, 0, S.st>>>(S.lv_nodes[0].p, S.d_total.p, batch_cap, C, kNumSMs, S.lv_item_off[0].p,
+                                                     S.lv_hitem_off[0].p, S.d_binfo.p, S.d_total.p + 1);
+        HAR_LAUNCH_CHECK();
+        t_prep += ms_since(t_a);
+        return dd_fetch_info(S, nb);
+    };
+    // one level of a set: wait for its launch data, enqueue its batches and the construction of the next level
+    auto dd_advance = [&](FitSet& S) -> int {
+        auto t_a = now();
+        HAR_CUDA(cudaEventSynchronize(S.ev));
+        S.inflight = false;
+        t_wait += ms_since(t_a);
+        t_a = now();
+        const int ncur = S.pin->h_n.p[0];
+        S.ncur = ncur;
+        if (ncur == 0) { S.done = true; return HAR_OK; }
+        const int L = S.level, cur = S.cur, nxt = cur ^ 1;
+        const int64_t nb = ceil_div(ncur, batch_cap);
+        const int64_t base = S.pool_used;
+        if ((size_t)(base + ncur) > S.cap_pool) {                       // grow the pool of finished nodes, keeping its content
+            const size_t ncap = std::max<size_t>((size_t)(base + ncur) * 2, 4096);
+            DevBuf<NodeResult> nr_; DevBuf<uint32_t> ns_; DevBuf<PoolMeta> nm_;
+            HAR_CUDA(nr_.alloc(ncap, S.st)); HAR_CUDA(ns_.alloc(ncap * 3 * C, S.st)); HAR_CUDA(nm_.alloc(ncap, S.st));
+            if (base > 0) {
+                HAR_CUDA(cudaMemcpyAsync(nr_.p, S.pool_res.p, sizeof(NodeResult) * base, cudaMemcpyDeviceToDevice, S.st));
+                HAR_CUDA(cudaMemcpyAsync(ns_.p, S.pool_stats.p, sizeof(uint32_t) * base * 3 * C, cudaMemcpyDeviceToDevice, S.st));
+                HAR_CUDA(cudaMemcpyAsync(nm_.p, S.pool_meta.p, sizeof(PoolMeta) * base, cudaMemcpyDeviceToDevice, S.st));
+            }
+            std::swap(S.pool_res.p, nr_.p); std::swap(S.pool_res.n, nr_.n); std::swap(S.pool_res.s, nr_.s);
+            std::swap(S.pool_stats.p, ns_.p); std::swap(S.pool_stats.n, ns_.n); std::swap(S.pool_stats.s, ns_.s);
+            std::swap(S.pool_meta.p, nm_.p); std::swap(S.pool_meta.n, nm_.n); std::swap(S.pool_meta.s, nm_.s);
+            S.cap_pool = ncap;
+        }
+        const bool last_level = L + 1 >= p->max_depth;                  // no child of this level can be split
+        const int32_t* loff_p = d_loff_all.p;
+        for (int64_t b = 0; b < nb; b++) {
+            const BatchInfo bi = S.pin->h_binfo.p[b];
+            const int ng = bi.ng;
+            if (ng <= 0) continue;
+            fo->num_batches++;
+            const size_t reduce_words = (size_t)bi.hb_direct + (size_t)ng * C;
+            const size_t need_hist = reduce_words + (size_t)bi.n_derived * full_len;
+            if (need_hist > S.cap_hist) { S.cap_hist = need_hist + need_hist / 4; HAR_CUDA(S.d_hist.alloc(S.cap_hist, S.st)); }
+            if ((size_t)bi.items + 1 > S.cap_items) { S.cap_items = (size_t)bi.items * 2 + 1; HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, S.st)); }
+            const NodeDesc* nodes = S.lv_nodes[cur].p + b * batch_cap;
+            const int32_t* io = S.lv_item_off[cur].p + b * (batch_cap + 1);
+            const int32_t* ho = S.lv_hitem_off[cur].p + b * (batch_cap + 1);
+            NodeResult* res = S.pool_res.p + base + b * batch_cap;
+            uint32_t* rstats = S.pool_stats.p + (base + b * batch_cap) * 3 * C;
+            uint32_t* d_parent = S.d_hist.p + bi.hb_direct;
+            HAR_CUDA(cudaMemsetAsync(S.d_hist.p, 0, sizeof(uint32_t) * reduce_words, S.st));
+            if (bi.hitems > 0) {
+                prof_begin(S.st);
+                k_node_hist<false><<<(unsigned)bi.hitems, HIST_THREADS, hist_smem, S.st>>>(nodes, ho, ng, bi.chunk_rows, d_bins.p, ldb,
+                    d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
+                HAR_LAUNCH_CHECK();
+                prof_end(PROF_NODE_HIST, S.st, (double)bi.hist_rows);
+            }
+            if (int rc = dist_allreduce(dist, S.d_hist.p, (int64_t)reduce_words, S.st)) return rc;
+            const unsigned copy_slices = (unsigned)std::max<int64_t>(1, std::min<int64_t>(8, full_len / 2048));
+            if (bi.n_derived > 0) {
+                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(nodes, C, S.d_hist.p, d_parent);
+                HAR_LAUNCH_CHECK();
+            }
+            prof_begin(S.st);
+            k_best_split<<<ng, BS_THREADS, bs_smem, S.st>>>(nodes, ng, S.d_hist.p, d_parent, nullptr, loff_p, 0, fm, res, rstats);
+            HAR_LAUNCH_CHECK();
+            prof_end(PROF_BEST_SPLIT, S.st, (double)ng);
+            if (!last_level) {
+                if (subtract && S.kept_slots[cur] > 0) {
+                    k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(nodes, res, C, S.d_hist.p, d_parent);
+                    HAR_LAUNCH_CHECK();
+                }
+                if (bi.items > 0) {
+                    prof_begin(S.st);
+                    k_part_count<<<(unsigned)bi.items, HIST_THREADS, 0, S.st>>>(nodes, io, ng, bi.chunk_rows, res, d_bins.p, ldb, n,
+                                                                               perm0.p, perm1.p, S.d_chunk_left.p);
+                    HAR_LAUNCH_CHECK();
+                    prof_end(PROF_PART_COUNT, S.st, (double)bi.rows_total);
+                    k_part_scan<<<(unsigned)ceil_div(ng, 4), 128, 0, S.st>>>(io, ng, res, S.d_chunk_left.p);
+                    HAR_LAUNCH_CHECK();
+                    prof_begin(S.st);
+                    k_part_scatter<<<(unsigned)bi.items, HIST_THREADS, 0, S.st>>>(nodes, io, ng, bi.chunk_rows, res, d_bins.p, ldb, n,
+                                                                                 perm0.p, perm1.p, S.d_chunk_left.p);
+                    HAR_LAUNCH_CHECK();
+                    prof_end(PROF_PART_SCATTER, S.st, (double)bi.rows_total);
+                }
+            }
+        }
+        S.pool_used = base + ncur;
+        // ---- the next level's node table, on the device ----
+        const int64_t next_upper = 2LL * ncur;
+        if (int rc = dd_ensure_level(S, nxt, next_upper)) return rc;
+        if (int rc = dd_ensure_kept(S, nxt, L + 1, next_upper)) return rc;
+        if ((size_t)ncur > S.cap_cnt) { S.cap_cnt = (size_t)ncur * 2; HAR_CUDA(S.d_cnt.alloc(S.cap_cnt, S.st)); }
+        const unsigned gb = (unsigned)ceil_div(ncur, 256);
+        k_grow_flags<<<gb, 256, 0, S.st>>>(S.lv_nodes[cur].p, S.pool_res.p + base, ncur, p->max_depth, S.d_cnt.p);
+        HAR_LAUNCH_CHECK();
+        k_grow_scan<<<1, 1024, 0, S.st>>>(S.d_cnt.p, ncur, S.d_total.p);
+        HAR_LAUNCH_CHECK();
+        k_grow_emit<<<gb, 256, 0, S.st>>>(S.lv_nodes[cur].p, S.pool_res.p + base, S.pool_stats.p + base * 3 * C, S.d_cnt.p, ncur, C,
+                                          p->max_depth, batch_cap, (int32_t)full_len, F, (int)(base + ncur), S.kept[nxt].p,
+                                          S.kept_slots[nxt], slot_words, S.pool_meta.p + base, S.lv_nodes[nxt].p);
+        HAR_LAUNCH_CHECK();
+        const int64_t nb_next = ceil_div(next_upper, batch_cap);
+        k_grow_layout<<<(unsigned)nb_next, 256, 0, S.st>>>(S.lv_nodes[nxt].p, S.d_total.p, batch_cap, C, kNumSMs, S.lv_item_off[nxt].p,
+                                                          S.lv_hitem_off[nxt].p, S.d_binfo.p, S.d_total.p + 1);
+        HAR_LAUNCH_CHECK();
+        S.level = L + 1; S.cur = nxt;
+        groups_run++;
+        t_prep += ms_since(t_a);
+        return dd_fetch_info(S, nb_next);
+    };
+    // finished nodes of a set -> host, then the per-tree LearningNode vectors the toNode stage reads
+    auto dd_finish = [&](FitSet& S) -> int {
+        const int64_t N = S.pool_used;
+        if (N == 0) return HAR_OK;
+        HAR_CUDA(S.pin->h_res.reserve(N)); HAR_CUDA(S.pin->h_res_stats.reserve((size_t)N * 3 * C)); HAR_CUDA(S.pin->h_meta.reserve(N));
+        HAR_CUDA(cudaMemcpyAsync(S.pin->h_res.p, S.pool_res.p, sizeof(NodeResult) * N, cudaMemcpyDeviceToHost, S.st));
+        HAR_CUDA(cudaMemcpyAsync(S.pin->h_res_stats.p, S.pool_stats.p, sizeof(uint32_t) * (size_t)N * 3 * C, cudaMemcpyDeviceToHost, S.st));
+        HAR_CUDA(cudaMemcpyAsync(S.pin->h_meta.p, S.pool_meta.p, sizeof(PoolMeta) * N, cudaMemcpyDeviceToHost, S.st));
+        HAR_CUDA(cudaEventRecord(S.ev, S.st));
+        return HAR_OK;
+    };
+    auto dd_build_trees = [&](FitSet& S) {
+        const NodeResult* R = S.pin->h_res.p;
+        const uint32_t* RS = S.pin->h_res_stats.p;
+        const PoolMeta* M = S.pin->h_meta.p;
+        parallel_for((int)S.my_trees.size(), S.pool_used >= 512, [&](int q) {
+            const int t = S.my_trees[q];
+            std::vector<LNode>& tr = trees[t];
+            std::vector<uint32_t>& ts = tree_stats[t];
+            std::vector<std::pair<int, int>> todo;                     // (pool index, LNode index), parents first
+            todo.emplace_back(q, 0);
+            for (size_t k = 0; k < todo.size(); k++) {
+                const int pi = todo[k].first, ni = todo[k].second;
+                const NodeResult& r = R[pi];
+                const uint32_t* rs = RS + (size_t)pi * 3 * C;
+                const int level = tr[ni].level;
+                const bool is_leaf = !(r.gain > 0.0) || level == p->max_depth;
+                {
+                    LNode& nd = tr[ni];
+                    nd.is_leaf = is_leaf; nd.valid = r.valid != 0; nd.gain = r.gain; nd.impurity = r.impurity;
+                    for (int c = 0; c < C; c++) ts[(size_t)ni * C + c] = rs[2 * C + c];
+                }
+                if (is_leaf) continue;
+                const bool child_leaf = level + 1 == p->max_depth;
+                const bool ll = child_leaf || r.left_imp == 0.0, rl = child_leaf || r.right_imp == 0.0;
+                const int li = (int)tr.size();
+                tr.emplace_back(); tr.emplace_back();
+                LNode& nd = tr[ni];
+                LNode& Lc = tr[li]; LNode& Rc = tr[li + 1];
+                Lc.id = nd.id * 2; Rc.id = Lc.id + 1;
+                Lc.parent = Rc.parent = ni;
+                Lc.level = Rc.level = level + 1;
+                Lc.is_leaf = ll; Rc.is_leaf = rl; Lc.impurity = r.left_imp; Rc.impurity = r.right_imp;
+                Lc.pushed = !ll; Rc.pushed = !rl;
+                ts.resize((size_t)(li + 2) * C);
+                for (int c = 0; c < C; c++) { ts[(size_t)li * C + c] = rs[c]; ts[(size_t)(li + 1) * C + c] = rs[C + c]; }
+                nd.left = li; nd.right = li + 1;
+                nd.feature = r.feature; nd.kind = r.kind; nd.split = r.split; nd.mask = r.left_mask; nd.arity = m.arity[r.feature];
+                nd.threshold = r.kind == KIND_CONT ? fo->thresholds[(size_t)r.feature * MB + r.split] : 0.0;
+                if (M[pi].left >= 0) todo.emplace_back(M[pi].left, li);
+                if (M[pi].right >= 0) todo.emplace_back(M[pi].right, li + 1);
+            }
+        });
+    };
+
+    if (device_grow) {
+        for (int k = 0; k < num_sets; k++) if (int rc = dd_start(sets[k])) return rc;
+        for (;;) {
+            bool any = false;
+            for (int k = 0; k < num_sets; k++) {
+                if (sets[k].done) continue;
+                if (int rc = dd_advance(sets[k])) return rc;
+                any = any || !sets[k].done;
+            }
+            if (!any) break;
+        }
+        for (int k = 0; k < num_sets; k++) if (int rc = dd_finish(sets[k])) return rc;
+        auto t_a = now();
+        for (int k = 0; k < num_sets; k++) {
+            if (sets[k].pool_used == 0) continue;
+            HAR_CUDA(cudaEventSynchronize(sets[k].ev));
+            dd_build_trees(sets[k]);
+        }
+        t_post += ms_since(t_a);
+    } else
     for (;;) {
         bool any = false;
         for (int k = 0; k < num_sets; k++) {
@@ -1043,7 +1348,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         if (!any) break;
     }
     for (int k = 0; k < num_sets; k++) HAR_CUDA(set_side[k].join(s));
-    if (num_sets == 1) fo->num_groups = groups_run;
+    const bool spark_order = num_sets == 1 && !device_grow;       // the groups that ran are Spark's groups
+    if (spark_order) fo->num_groups = groups_run;
     auto t_emit = now();
 
     // ---- toNode(prune = true): per tree in parallel, then concatenated in tree order ----
@@ -1088,7 +1394,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         });
     }
     fo->tree_off[T] = (int64_t)fo->feature.size();
-    if (num_sets > 1) {
+    if (!spark_order) {
         // Spark's node-group count is not needed to train or predict: recount it on demand (har_forest_fit_info)
         auto kept = std::make_shared<std::vector<std::vector<LNode>>>(std::move(trees));
         const int64_t cost = (int64_t)C * total_bins_all * 8, max_mem = p->max_memory_bytes;
