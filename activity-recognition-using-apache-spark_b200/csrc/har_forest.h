@@ -28,5 +28,21 @@ struct har_forest {
     double* d_leaf = nullptr;     // [num_leaves][C]: DT = class counts, RF = counts / total
     int64_t* d_roots = nullptr;   // [T] index of each tree's root in d_nodes
     int leaf_mode = -1;           // is_forest flag the leaf table was built for
+    // Fits that grew the trees on the device (har_tree_fit.cu) write the tables above straight from the device-side
+    // node pool; per-slot class counts stay on the device so the leaf table can be rebuilt for the other predict mode.
+    // The flat host arrays are then filled on first use (har_forest_export / import paths) by `materialize`.
+    uint32_t* d_slot_stats = nullptr;   // [num_slots][C]
+    int64_t num_slots = 0;
+    int64_t total_nodes = -1;     // pruned node count, known before the host arrays exist
+    mutable std::function<int()> materialize;
     int max_depth = 0;
 };
+
+// Fill the flat host arrays if the fit left them on the device.  Returns 0 (HAR_OK) or the error of the read-back.
+inline int har_forest_ensure_host(const har_forest* f) {
+    std::lock_guard<std::mutex> lk(f->count_mu);
+    if (!f->materialize) return 0;
+    const int rc = f->materialize();
+    if (rc == 0) f->materialize = nullptr;
+    return rc;
+}

@@ -13,15 +13,11 @@
 
 #include "har_common.cuh"
 #include "har_forest.h"
+#include "har_pnode.cuh"
 
 namespace {
 
-struct __align__(16) PNode {
-    int32_t feature;     // < 0: leaf.  bit 30: categorical, bit 29: values outside the mask domain go left
-    int32_t left;        // internal: index of the left child (right = left + 1); leaf: leaf-vector index
-    union { double thr; unsigned long long mask; };
-};
-constexpr int32_t P_CAT = 1 << 30, P_DEFLEFT = 1 << 29, P_FMASK = (1 << 29) - 1;
+using har::PNode; using har::P_CAT; using har::P_DEFLEFT; using har::P_FMASK;
 constexpr int PRED_THREADS = 128;
 
 template <bool STAGE>
@@ -90,13 +86,26 @@ void free_device_tables(har_forest* f) {
     if (f->d_nodes) cudaFree(f->d_nodes);
     if (f->d_leaf) cudaFree(f->d_leaf);
     if (f->d_roots) cudaFree(f->d_roots);
-    f->d_nodes = nullptr; f->d_leaf = nullptr; f->d_roots = nullptr; f->dev = -1; f->leaf_mode = -1;
+    if (f->d_slot_stats) cudaFree(f->d_slot_stats);
+    f->d_nodes = nullptr; f->d_leaf = nullptr; f->d_roots = nullptr; f->d_slot_stats = nullptr; f->num_slots = 0;
+    f->dev = -1; f->leaf_mode = -1;
 }
 
 int build_device_tables(har_forest* f, int is_forest, cudaStream_t s) {
     int dev = 0;
     HAR_CUDA(cudaGetDevice(&dev));
     if (f->d_nodes && f->dev == dev && f->leaf_mode == is_forest) return HAR_OK;
+    if (f->d_nodes && f->dev == dev && f->d_slot_stats) {
+        // tables written by the fit on this device: only the leaf vectors depend on the predict mode
+        har::pool_setup();
+        if (!f->d_leaf) HAR_CUDA(cudaMallocAsync((void**)&f->d_leaf, sizeof(double) * std::max<int64_t>(f->num_slots * f->C, 1), s));
+        har::k_fin_leaf_table<<<(unsigned)har::ceil_div(std::max<int64_t>(f->num_slots, 1), 256), 256, 0, s>>>(
+            f->d_slot_stats, f->num_slots, f->C, is_forest, f->d_leaf);
+        HAR_LAUNCH_CHECK();
+        f->leaf_mode = is_forest;
+        return HAR_OK;
+    }
+    if (int rc = har_forest_ensure_host(f)) return rc;
     free_device_tables(f);
     const int T = f->T, C = f->C;
     const int64_t N = (int64_t)f->feature.size();
@@ -132,13 +141,7 @@ int build_device_tables(har_forest* f, int is_forest, cudaStream_t s) {
                 const int ar = f->arity[src];
                 d.feature = f->feature[src];
                 if (ar > 0) {
-                    // CategoricalSplit keeps the smaller side: isLeft = |left| <= arity / 2 (Split.scala)
-                    const unsigned long long lm = f->left_mask[src];
-                    const unsigned long long dom = ar >= 64 ? ~0ULL : ((1ULL << ar) - 1);
-                    const bool is_left = __builtin_popcountll(lm & dom) <= ar / 2;
-                    d.feature |= P_CAT;
-                    if (is_left) d.mask = lm & dom;
-                    else { d.mask = (lm & dom) | ~dom; d.feature |= P_DEFLEFT; }
+                    har::pnode_set_categorical(d, f->feature[src], ar, f->left_mask[src]);
                 } else {
                     d.thr = f->threshold[src];
                 }

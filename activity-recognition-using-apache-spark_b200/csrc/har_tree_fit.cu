@@ -408,6 +408,144 @@ int64_t emit_node(har_forest& fo, const std::vector<LNode>& tree, const std::vec
     return me - base;
 }
 
+// LearningNode.toNode(prune = true) for every tree (in parallel), concatenated in tree order into the flat arrays
+void emit_forest(har_forest* fo, int T, int C, const std::vector<std::vector<LNode>>& trees,
+                 const std::vector<std::vector<uint32_t>>& tree_stats, bool trace) {
+    const auto t_emit = std::chrono::steady_clock::now();
+    fo->tree_off.assign(T + 1, 0);
+    {
+        std::vector<har_forest> parts(T);
+        parallel_for(T, true, [&](int t) {
+            har_forest& pf = parts[t];
+            pf.C = C;
+            const size_t nn = trees[t].size();
+            pf.feature.reserve(nn); pf.left.reserve(nn); pf.right.reserve(nn); pf.node_id.reserve(nn); pf.arity.reserve(nn);
+            pf.threshold.reserve(nn); pf.left_mask.reserve(nn); pf.prediction.reserve(nn); pf.impurity.reserve(nn);
+            pf.gain.reserve(nn); pf.stats.reserve(nn * C);
+            bool leaf = false;
+            emit_node(pf, trees[t], tree_stats[t], 0, 0, &leaf);
+        });
+        if (trace) fprintf(stderr, "[har_forest_fit]   toNode: parallel emit %.2f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_emit).count());
+        size_t total_nodes = 0;
+        for (int t = 0; t < T; t++) { fo->tree_off[t] = (int64_t)total_nodes; total_nodes += parts[t].feature.size(); }
+        // one host thread per output array: the first touch of the fresh allocations (page faults) and the copies
+        // run in parallel instead of serialising ~12 MB of inserts
+        har_forest* fp = fo;
+        auto cat = [&](auto har_forest::*member, size_t per_node) {
+            auto& dst = fp->*member;
+            dst.reserve(total_nodes * per_node);
+            for (int t = 0; t < T; t++) { const auto& src = parts[t].*member; dst.insert(dst.end(), src.begin(), src.end()); }
+        };
+        parallel_for(11, true, [&](int k) {
+            switch (k) {
+                case 0: cat(&har_forest::stats, (size_t)C); break;
+                case 1: cat(&har_forest::feature, 1); break;
+                case 2: cat(&har_forest::left, 1); break;
+                case 3: cat(&har_forest::right, 1); break;
+                case 4: cat(&har_forest::node_id, 1); break;
+                case 5: cat(&har_forest::arity, 1); break;
+                case 6: cat(&har_forest::threshold, 1); break;
+                case 7: cat(&har_forest::left_mask, 1); break;
+                case 8: cat(&har_forest::prediction, 1); break;
+                case 9: cat(&har_forest::impurity, 1); break;
+                default: cat(&har_forest::gain, 1); break;
+            }
+        });
+    }
+    fo->tree_off[T] = (int64_t)fo->feature.size();
+    fo->total_nodes = (int64_t)fo->feature.size();
+}
+
+// ---- read-back of trees grown on the device ---------------------------------------------------------------
+// The device-driven fit leaves the trained nodes in per-set pools on the GPU (level order; see k_grow_* / k_fin_*)
+// and writes the predict tables from them.  Everything the *host* may still want — the flat model arrays of
+// har_forest_export, Spark's node-group count — is rebuilt from the pools on first use.
+void build_tree_from_pool(std::vector<LNode>& tr, std::vector<uint32_t>& ts, int root_pool_idx, const NodeResult* R,
+                          const uint32_t* RS, const PoolMeta* M, int C, int max_depth, const std::vector<int32_t>& arity,
+                          const std::vector<double>& thresholds, int MB) {
+    tr.clear(); tr.emplace_back();                                     // root: id 1, level 0
+    ts.assign(C, 0);
+    std::vector<std::pair<int, int>> todo;                             // (pool index, LNode index), parents first
+    todo.emplace_back(root_pool_idx, 0);
+    for (size_t k = 0; k < todo.size(); k++) {
+        const int pi = todo[k].first, ni = todo[k].second;
+        const NodeResult& r = R[pi];
+        const uint32_t* rs = RS + (size_t)pi * 3 * C;
+        const int level = tr[ni].level;
+        const bool is_leaf = !(r.gain > 0.0) || level == max_depth;
+        {
+            LNode& nd = tr[ni];
+            nd.is_leaf = is_leaf; nd.valid = r.valid != 0; nd.gain = r.gain; nd.impurity = r.impurity;
+            for (int c = 0; c < C; c++) ts[(size_t)ni * C + c] = rs[2 * C + c];
+        }
+        if (is_leaf) continue;
+        const bool child_leaf = level + 1 == max_depth;
+        const bool ll = child_leaf || r.left_imp == 0.0, rl = child_leaf || r.right_imp == 0.0;
+        const int li = (int)tr.size();
+        tr.emplace_back(); tr.emplace_back();
+        LNode& nd = tr[ni];
+        LNode& Lc = tr[li]; LNode& Rc = tr[li + 1];
+        Lc.id = nd.id * 2; Rc.id = Lc.id + 1;
+        Lc.parent = Rc.parent = ni;
+        Lc.level = Rc.level = level + 1;
+        Lc.is_leaf = ll; Rc.is_leaf = rl; Lc.impurity = r.left_imp; Rc.impurity = r.right_imp;
+        Lc.pushed = !ll; Rc.pushed = !rl;
+        ts.resize((size_t)(li + 2) * C);
+        for (int c = 0; c < C; c++) { ts[(size_t)li * C + c] = rs[c]; ts[(size_t)(li + 1) * C + c] = rs[C + c]; }
+        nd.left = li; nd.right = li + 1;
+        nd.feature = r.feature; nd.kind = r.kind; nd.split = r.split; nd.mask = r.left_mask; nd.arity = arity[r.feature];
+        nd.threshold = r.kind == KIND_CONT ? thresholds[(size_t)r.feature * MB + r.split] : 0.0;
+        if (M[pi].left >= 0) todo.emplace_back(M[pi].left, li);
+        if (M[pi].right >= 0) todo.emplace_back(M[pi].right, li + 1);
+    }
+}
+
+struct LazyPools {
+    int T = 0, C = 0, MB = 0, max_depth = 0, num_sets = 0, dev = 0;
+    std::vector<int32_t> arity;
+    std::vector<double> thresholds;
+    struct SetPool {
+        std::vector<int> my_trees;
+        int64_t N = 0;
+        NodeResult* res = nullptr; uint32_t* stats = nullptr; PoolMeta* meta = nullptr;     // device, owned
+    } set[2];
+    std::mutex mu;
+    bool built = false;
+    std::vector<std::vector<LNode>> trees;
+    std::vector<std::vector<uint32_t>> tree_stats;
+    ~LazyPools() {
+        for (auto& sp : set) { if (sp.res) cudaFree(sp.res); if (sp.stats) cudaFree(sp.stats); if (sp.meta) cudaFree(sp.meta); }
+    }
+    // pools -> host -> per-tree LearningNode vectors (once); the device copies are released afterwards
+    int build() {
+        std::lock_guard<std::mutex> lk(mu);
+        if (built) return HAR_OK;
+        int cur = 0;
+        HAR_CUDA(cudaGetDevice(&cur));
+        if (cur != dev) HAR_CUDA(cudaSetDevice(dev));
+        trees.assign(T, {}); tree_stats.assign(T, {});
+        for (int k = 0; k < num_sets; k++) {
+            SetPool& sp = set[k];
+            if (sp.N == 0) continue;
+            std::vector<NodeResult> R((size_t)sp.N);
+            std::vector<uint32_t> RS((size_t)sp.N * 3 * C);
+            std::vector<PoolMeta> M((size_t)sp.N);
+            HAR_CUDA(cudaMemcpy(R.data(), sp.res, sizeof(NodeResult) * sp.N, cudaMemcpyDeviceToHost));
+            HAR_CUDA(cudaMemcpy(RS.data(), sp.stats, sizeof(uint32_t) * (size_t)sp.N * 3 * C, cudaMemcpyDeviceToHost));
+            HAR_CUDA(cudaMemcpy(M.data(), sp.meta, sizeof(PoolMeta) * sp.N, cudaMemcpyDeviceToHost));
+            parallel_for((int)sp.my_trees.size(), sp.N >= 512, [&](int q) {
+                const int t = sp.my_trees[q];
+                build_tree_from_pool(trees[t], tree_stats[t], q, R.data(), RS.data(), M.data(), C, max_depth, arity, thresholds, MB);
+            });
+            cudaFree(sp.res); cudaFree(sp.stats); cudaFree(sp.meta);
+            sp.res = nullptr; sp.stats = nullptr; sp.meta = nullptr;
+        }
+        if (cur != dev) cudaSetDevice(cur);
+        built = true;
+        return HAR_OK;
+    }
+};
+
 template <typename T>
 struct Pinned {
     T* p = nullptr;
@@ -717,6 +855,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         // device-driven growth (all-features fits): node tables of two consecutive levels, per-batch launch data,
         // the pool of finished nodes and the kept counters of two consecutive levels
         std::vector<int> my_trees;
+        std::vector<std::pair<int64_t, int>> levels;         // (first pool index, nodes) of every trained level
         DevBuf<NodeDesc> lv_nodes[2];
         DevBuf<int32_t> lv_item_off[2], lv_hitem_off[2], d_cnt, d_total;      // d_total: [children in total, copy for the host]
         DevBuf<BatchInfo> d_binfo;
@@ -1240,6 +1379,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             }
         }
         S.pool_used = base + ncur;
+        S.levels.emplace_back(base, ncur);
         // ---- the next level's node table, on the device ----
         const int64_t next_upper = 2LL * ncur;
         if (int rc = dd_ensure_level(S, nxt, next_upper)) return rc;
@@ -1263,61 +1403,6 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         t_prep += ms_since(t_a);
         return dd_fetch_info(S, nb_next);
     };
-    // finished nodes of a set -> host, then the per-tree LearningNode vectors the toNode stage reads
-    auto dd_finish = [&](FitSet& S) -> int {
-        const int64_t N = S.pool_used;
-        if (N == 0) return HAR_OK;
-        HAR_CUDA(S.pin->h_res.reserve(N)); HAR_CUDA(S.pin->h_res_stats.reserve((size_t)N * 3 * C)); HAR_CUDA(S.pin->h_meta.reserve(N));
-        HAR_CUDA(cudaMemcpyAsync(S.pin->h_res.p, S.pool_res.p, sizeof(NodeResult) * N, cudaMemcpyDeviceToHost, S.st));
-        HAR_CUDA(cudaMemcpyAsync(S.pin->h_res_stats.p, S.pool_stats.p, sizeof(uint32_t) * (size_t)N * 3 * C, cudaMemcpyDeviceToHost, S.st));
-        HAR_CUDA(cudaMemcpyAsync(S.pin->h_meta.p, S.pool_meta.p, sizeof(PoolMeta) * N, cudaMemcpyDeviceToHost, S.st));
-        HAR_CUDA(cudaEventRecord(S.ev, S.st));
-        return HAR_OK;
-    };
-    auto dd_build_trees = [&](FitSet& S) {
-        const NodeResult* R = S.pin->h_res.p;
-        const uint32_t* RS = S.pin->h_res_stats.p;
-        const PoolMeta* M = S.pin->h_meta.p;
-        parallel_for((int)S.my_trees.size(), S.pool_used >= 512, [&](int q) {
-            const int t = S.my_trees[q];
-            std::vector<LNode>& tr = trees[t];
-            std::vector<uint32_t>& ts = tree_stats[t];
-            std::vector<std::pair<int, int>> todo;                     // (pool index, LNode index), parents first
-            todo.emplace_back(q, 0);
-            for (size_t k = 0; k < todo.size(); k++) {
-                const int pi = todo[k].first, ni = todo[k].second;
-                const NodeResult& r = R[pi];
-                const uint32_t* rs = RS + (size_t)pi * 3 * C;
-                const int level = tr[ni].level;
-                const bool is_leaf = !(r.gain > 0.0) || level == p->max_depth;
-                {
-                    LNode& nd = tr[ni];
-                    nd.is_leaf = is_leaf; nd.valid = r.valid != 0; nd.gain = r.gain; nd.impurity = r.impurity;
-                    for (int c = 0; c < C; c++) ts[(size_t)ni * C + c] = rs[2 * C + c];
-                }
-                if (is_leaf) continue;
-                const bool child_leaf = level + 1 == p->max_depth;
-                const bool ll = child_leaf || r.left_imp == 0.0, rl = child_leaf || r.right_imp == 0.0;
-                const int li = (int)tr.size();
-                tr.emplace_back(); tr.emplace_back();
-                LNode& nd = tr[ni];
-                LNode& Lc = tr[li]; LNode& Rc = tr[li + 1];
-                Lc.id = nd.id * 2; Rc.id = Lc.id + 1;
-                Lc.parent = Rc.parent = ni;
-                Lc.level = Rc.level = level + 1;
-                Lc.is_leaf = ll; Rc.is_leaf = rl; Lc.impurity = r.left_imp; Rc.impurity = r.right_imp;
-                Lc.pushed = !ll; Rc.pushed = !rl;
-                ts.resize((size_t)(li + 2) * C);
-                for (int c = 0; c < C; c++) { ts[(size_t)li * C + c] = rs[c]; ts[(size_t)(li + 1) * C + c] = rs[C + c]; }
-                nd.left = li; nd.right = li + 1;
-                nd.feature = r.feature; nd.kind = r.kind; nd.split = r.split; nd.mask = r.left_mask; nd.arity = m.arity[r.feature];
-                nd.threshold = r.kind == KIND_CONT ? fo->thresholds[(size_t)r.feature * MB + r.split] : 0.0;
-                if (M[pi].left >= 0) todo.emplace_back(M[pi].left, li);
-                if (M[pi].right >= 0) todo.emplace_back(M[pi].right, li + 1);
-            }
-        });
-    };
-
     if (device_grow) {
         for (int k = 0; k < num_sets; k++) if (int rc = dd_start(sets[k])) return rc;
         for (;;) {
@@ -1329,14 +1414,6 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             }
             if (!any) break;
         }
-        for (int k = 0; k < num_sets; k++) if (int rc = dd_finish(sets[k])) return rc;
-        auto t_a = now();
-        for (int k = 0; k < num_sets; k++) {
-            if (sets[k].pool_used == 0) continue;
-            HAR_CUDA(cudaEventSynchronize(sets[k].ev));
-            dd_build_trees(sets[k]);
-        }
-        t_post += ms_since(t_a);
     } else
     for (;;) {
         bool any = false;
@@ -1353,58 +1430,98 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     auto t_emit = now();
 
     // ---- toNode(prune = true): per tree in parallel, then concatenated in tree order ----
-    fo->tree_off.assign(T + 1, 0);
-    {
-        std::vector<har_forest> parts(T);
-        parallel_for(T, true, [&](int t) {
-            har_forest& pf = parts[t];
-            pf.C = C;
-            const size_t nn = trees[t].size();
-            pf.feature.reserve(nn); pf.left.reserve(nn); pf.right.reserve(nn); pf.node_id.reserve(nn); pf.arity.reserve(nn);
-            pf.threshold.reserve(nn); pf.left_mask.reserve(nn); pf.prediction.reserve(nn); pf.impurity.reserve(nn);
-            pf.gain.reserve(nn); pf.stats.reserve(nn * C);
-            bool leaf = false;
-            emit_node(pf, trees[t], tree_stats[t], 0, 0, &leaf);
-        });
-        if (trace) fprintf(stderr, "[har_forest_fit]   toNode: parallel emit %.2f ms\n", ms_since(t_emit));
-        size_t total_nodes = 0;
-        for (int t = 0; t < T; t++) { fo->tree_off[t] = (int64_t)total_nodes; total_nodes += parts[t].feature.size(); }
-        // one host thread per output array: the first touch of the fresh allocations (page faults) and the copies
-        // run in parallel instead of serialising ~12 MB of inserts
-        har_forest* fp = fo.get();
-        auto cat = [&](auto har_forest::*member, size_t per_node) {
-            auto& dst = fp->*member;
-            dst.reserve(total_nodes * per_node);
-            for (int t = 0; t < T; t++) { const auto& src = parts[t].*member; dst.insert(dst.end(), src.begin(), src.end()); }
-        };
-        parallel_for(11, true, [&](int k) {
-            switch (k) {
-                case 0: cat(&har_forest::stats, (size_t)C); break;
-                case 1: cat(&har_forest::feature, 1); break;
-                case 2: cat(&har_forest::left, 1); break;
-                case 3: cat(&har_forest::right, 1); break;
-                case 4: cat(&har_forest::node_id, 1); break;
-                case 5: cat(&har_forest::arity, 1); break;
-                case 6: cat(&har_forest::threshold, 1); break;
-                case 7: cat(&har_forest::left_mask, 1); break;
-                case 8: cat(&har_forest::prediction, 1); break;
-                case 9: cat(&har_forest::impurity, 1); break;
-                default: cat(&har_forest::gain, 1); break;
+    if (!device_grow) {
+        emit_forest(fo.get(), T, C, trees, tree_stats, trace);
+        if (!spark_order) {
+            // Spark's node-group count is not needed to train or predict: recount it on demand (har_forest_fit_info)
+            auto kept = std::make_shared<std::vector<std::vector<LNode>>>(std::move(trees));
+            const int64_t cost = (int64_t)C * total_bins_all * 8, max_mem = p->max_memory_bytes;
+            fo->count_groups = [kept, cost, max_mem]() { return simulate_groups(*kept, cost, max_mem); };
+        }
+    } else {
+        // ---- toNode(prune = true) on the device, straight into the predict tables (k_fin_*) ----
+        int64_t npool_all = 0;
+        for (int k = 0; k < num_sets; k++) npool_all += sets[k].pool_used;
+        const int64_t slots_cap = (int64_t)T + 2 * npool_all;
+        har_forest* f = fo.get();
+        int dev_now = 0;
+        HAR_CUDA(cudaGetDevice(&dev_now));
+        HAR_CUDA(cudaMallocAsync(&f->d_nodes, sizeof(PNode) * slots_cap, s));
+        HAR_CUDA(cudaMallocAsync((void**)&f->d_slot_stats, sizeof(uint32_t) * slots_cap * C, s));
+        HAR_CUDA(cudaMallocAsync((void**)&f->d_roots, sizeof(int64_t) * T, s));
+        f->dev = dev_now; f->leaf_mode = -1;
+        DevBuf<double> d_thr; DevBuf<int32_t> d_ar, d_tot;
+        HAR_CUDA(d_thr.alloc((size_t)F * MB, s)); HAR_CUDA(d_ar.alloc(F, s)); HAR_CUDA(d_tot.alloc(2, s));
+        HAR_CUDA(cudaMemcpyAsync(d_thr.p, fo->thresholds.data(), sizeof(double) * (size_t)F * MB, cudaMemcpyHostToDevice, s));
+        HAR_CUDA(cudaMemcpyAsync(d_ar.p, m.arity.data(), sizeof(int32_t) * F, cudaMemcpyHostToDevice, s));
+        HAR_CUDA(cudaMemsetAsync(d_tot.p, 0, sizeof(int32_t) * 2, s));
+        std::vector<int64_t> roots(T);
+        for (int t = 0; t < T; t++) roots[t] = t;
+        HAR_CUDA(cudaMemcpyAsync(f->d_roots, roots.data(), sizeof(int64_t) * T, cudaMemcpyHostToDevice, s));
+        DevBuf<uint8_t> d_leafflag[2], d_alive[2];
+        DevBuf<int32_t> d_pred[2], d_rank[2], d_slot[2];
+        for (int k = 0; k < num_sets; k++) {
+            FitSet& S = sets[k];
+            const int np = (int)S.pool_used, nroots = (int)S.my_trees.size();
+            if (np == 0) continue;
+            HAR_CUDA(d_leafflag[k].alloc(np, s)); HAR_CUDA(d_alive[k].alloc(np, s));
+            HAR_CUDA(d_pred[k].alloc(np, s)); HAR_CUDA(d_rank[k].alloc(np, s)); HAR_CUDA(d_slot[k].alloc(np, s));
+            HAR_CUDA(cudaMemsetAsync(d_alive[k].p, 0, np, s));
+            HAR_CUDA(cudaMemsetAsync(d_alive[k].p, 1, nroots, s));
+            for (int L = (int)S.levels.size() - 1; L >= 0; L--) {
+                const int base = (int)S.levels[L].first, nl = S.levels[L].second;
+                k_fin_prune<<<(unsigned)ceil_div(nl, 256), 256, 0, s>>>(S.pool_res.p, S.pool_stats.p, S.pool_meta.p, base, nl, L,
+                                                                       p->max_depth, C, d_leafflag[k].p, d_pred[k].p);
+                HAR_LAUNCH_CHECK();
             }
-        });
-    }
-    fo->tree_off[T] = (int64_t)fo->feature.size();
-    if (!spark_order) {
-        // Spark's node-group count is not needed to train or predict: recount it on demand (har_forest_fit_info)
-        auto kept = std::make_shared<std::vector<std::vector<LNode>>>(std::move(trees));
+            for (int L = 0; L < (int)S.levels.size(); L++) {
+                const int base = (int)S.levels[L].first, nl = S.levels[L].second;
+                k_fin_alive<<<(unsigned)ceil_div(nl, 256), 256, 0, s>>>(S.pool_meta.p, base, nl, d_leafflag[k].p, d_alive[k].p, d_rank[k].p);
+                HAR_LAUNCH_CHECK();
+            }
+            k_grow_scan<<<1, 1024, 0, s>>>(d_rank[k].p, np, d_tot.p + k);
+            HAR_LAUNCH_CHECK();
+            const int32_t* rank_base = k == 0 ? nullptr : d_tot.p;
+            const unsigned gb = (unsigned)ceil_div(np, 256);
+            k_fin_children<<<gb, 256, 0, s>>>(S.pool_meta.p, S.pool_stats.p, np, nroots, d_rank[k].p, rank_base, T, C, d_alive[k].p,
+                                              d_leafflag[k].p, d_slot[k].p, (PNode*)f->d_nodes, f->d_slot_stats);
+            HAR_LAUNCH_CHECK();
+            k_fin_nodes<<<gb, 256, 0, s>>>(S.pool_res.p, S.pool_stats.p, np, d_rank[k].p, rank_base, T, C, d_alive[k].p, d_leafflag[k].p,
+                                           d_slot[k].p, d_thr.p, MB, d_ar.p, (PNode*)f->d_nodes, f->d_slot_stats);
+            HAR_LAUNCH_CHECK();
+        }
+        int32_t h_tot[2] = {0, 0};
+        HAR_CUDA(cudaMemcpyAsync(h_tot, d_tot.p, sizeof h_tot, cudaMemcpyDeviceToHost, s));
+        HAR_CUDA(cudaStreamSynchronize(s));
+        f->total_nodes = (int64_t)T + 2 * ((int64_t)h_tot[0] + h_tot[1]);
+        f->num_slots = f->total_nodes;
+        // the pools move into the forest: flat host arrays and Spark's group count are rebuilt from them on demand
+        auto lazy = std::make_shared<LazyPools>();
+        lazy->T = T; lazy->C = C; lazy->MB = MB; lazy->max_depth = p->max_depth; lazy->num_sets = num_sets; lazy->dev = dev_now;
+        lazy->arity = m.arity; lazy->thresholds = fo->thresholds;
+        for (int k = 0; k < num_sets; k++) {
+            FitSet& S = sets[k];
+            LazyPools::SetPool& sp = lazy->set[k];
+            sp.my_trees = S.my_trees; sp.N = S.pool_used;
+            sp.res = S.pool_res.p; sp.stats = S.pool_stats.p; sp.meta = S.pool_meta.p;
+            S.pool_res.p = nullptr; S.pool_stats.p = nullptr; S.pool_meta.p = nullptr;
+        }
         const int64_t cost = (int64_t)C * total_bins_all * 8, max_mem = p->max_memory_bytes;
-        fo->count_groups = [kept, cost, max_mem]() { return simulate_groups(*kept, cost, max_mem); };
+        fo->count_groups = [lazy, cost, max_mem]() -> int64_t {
+            if (lazy->build() != HAR_OK) return -1;
+            return simulate_groups(lazy->trees, cost, max_mem);
+        };
+        fo->materialize = [lazy, f, T, C, trace]() -> int {
+            if (int rc = lazy->build()) return rc;
+            emit_forest(f, T, C, lazy->trees, lazy->tree_stats, trace);
+            return HAR_OK;
+        };
     }
     fo->num_launches = launches_since_reset() - launches0;
     if (trace)
         fprintf(stderr, "[har_forest_fit] setup %.2f ms | loop: host prep+launch %.2f, gpu wait %.2f, driver-side %.2f | toNode %.2f | "
                         "total %.2f ms, %lld groups run, %lld batches, %zu nodes\n", t_setup, t_prep, t_wait, t_post, ms_since(t_emit),
-                ms_since(t_begin), (long long)groups_run, (long long)fo->num_batches, fo->feature.size());
+                ms_since(t_begin), (long long)groups_run, (long long)fo->num_batches, (size_t)fo->total_nodes);
     (void)world;
     *out = fo.release();
     return HAR_OK;
@@ -1416,7 +1533,7 @@ HAR_API int har_forest_shape(const har_forest_t* f, int32_t* num_trees, int32_t*
     if (num_trees) *num_trees = f->T;
     if (num_classes) *num_classes = f->C;
     if (num_features) *num_features = f->F;
-    if (total_nodes) *total_nodes = (int64_t)f->feature.size();
+    if (total_nodes) *total_nodes = f->total_nodes >= 0 ? f->total_nodes : (int64_t)f->feature.size();
     return HAR_OK;
 }
 
@@ -1424,6 +1541,7 @@ HAR_API int har_forest_export(const har_forest_t* f, int64_t* tree_off, int32_t*
                               int32_t* node_id, int32_t* arity, double* threshold, uint64_t* left_mask, double* prediction,
                               double* impurity, double* gain, double* stats) {
     if (!f) return fail(HAR_E_INVALID, "har_forest_export: NULL forest");
+    if (int rc = har_forest_ensure_host(f)) return rc;
     const size_t N = f->feature.size();
     if (tree_off) std::copy(f->tree_off.begin(), f->tree_off.end(), tree_off);
     if (feature) std::copy(f->feature.begin(), f->feature.end(), feature);
