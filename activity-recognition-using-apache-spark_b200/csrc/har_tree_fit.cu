@@ -1574,3 +1574,15 @@ HAR_API int har_forest_fit_info(const har_forest_t* f, double* thresholds, int32
     if (num_kernel_launches) *num_kernel_launches = f->num_launches;
     return HAR_OK;
 }
+
+// bit-for-bit comparison of the count division used by k_best_split with __ddiv_rn over n pseudo-random operand pairs
+HAR_API int har_debug_div_check(long long n, unsigned long long seed, unsigned long long* mismatches, har_stream_t stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    DevBuf<unsigned long long> d;
+    HAR_CUDA(d.alloc(1, s));
+    HAR_CUDA(cudaMemsetAsync(d.p, 0, sizeof(unsigned long long), s));
+    if (n > 0) { k_div_check<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(n, seed, d.p); HAR_LAUNCH_CHECK(); }
+    HAR_CUDA(cudaMemcpyAsync(mismatches, d.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    HAR_CUDA(cudaStreamSynchronize(s));
+    return HAR_OK;
+}

@@ -60,6 +60,7 @@ _SIGS = {
     "har_stream_synchronize": (C.c_int, [C.c_void_p]),
     "har_debug_launch_count": (C.c_longlong, [C.c_int]),
     "har_debug_comm_stats": (None, [C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), C.POINTER(C.c_int), C.c_int]),
+    "har_debug_div_check": (C.c_int, [C.c_longlong, C.c_ulonglong, C.POINTER(C.c_ulonglong), C.c_void_p]),
     "har_debug_smem_atomic_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double), C.c_void_p]),
     "har_debug_profile_enable": (None, [C.c_int]),
     "har_debug_profile_reset": (None, []),

@@ -85,6 +85,14 @@ def comm_stats(reset=False):
     return int(c.value), int(b.value), int(v.value)
 
 
+def div_check(n, seed=1):
+    """Mismatches between the count division of the best-split kernel and __ddiv_rn over n operand pairs."""
+    require_cuda()
+    m = C.c_ulonglong()
+    N.check(N.lib().har_debug_div_check(int(n), int(seed), C.byref(m), stream()))
+    return int(m.value)
+
+
 def launch_count(reset=False):
     return int(N.lib().har_debug_launch_count(1 if reset else 0))
 
