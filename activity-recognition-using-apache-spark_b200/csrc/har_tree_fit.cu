@@ -572,6 +572,16 @@ struct SideStream {
         if (ev_join) cudaEventDestroy(ev_join);
         if (s) cudaStreamDestroy(s);
     }
+    cudaError_t start() {                               // independent of any other stream
+        cudaError_t e;
+        if (!s) {
+            if ((e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)) != cudaSuccess) return e;
+            if ((e = cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming)) != cudaSuccess) return e;
+            if ((e = cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming)) != cudaSuccess) return e;
+        }
+        active = true;
+        return cudaSuccess;
+    }
     cudaError_t fork(cudaStream_t main) {
         cudaError_t e;
         if (!s) {
@@ -698,26 +708,14 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     if (int rc = build_meta(m, F, C, n_global, MB, arity)) return rc;
 
     // labels -> u8 (Classifier.extractLabeledPoints validation)
-    DevBuf<uint8_t> d_lab; DevBuf<unsigned long long> d_bad;
-    HAR_CUDA(d_lab.alloc(std::max<int64_t>(n, 1), s)); HAR_CUDA(d_bad.alloc(1, s));
-    HAR_CUDA(cudaMemsetAsync(d_bad.p, 0xff, sizeof(unsigned long long), s));
-    if (n) { k_labels_to_u8<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(d_y, n, C, d_lab.p, d_bad.p); HAR_LAUNCH_CHECK(); }
-    unsigned long long h_bad = 0;
-    HAR_CUDA(cudaMemcpyAsync(&h_bad, d_bad.p, sizeof h_bad, cudaMemcpyDeviceToHost, s));
-    HAR_CUDA(cudaStreamSynchronize(s));
-    if (h_bad != ~0ULL) {
-        double v = 0;
-        cudaMemcpy(&v, d_y + h_bad, sizeof(double), cudaMemcpyDeviceToHost);
-        return fail(HAR_E_INVALID, "Classifier given dataset with invalid label %g.  Labels must be integers in range [0, %d).", v, C);
-    }
-
-    // Bagging depends only on (n, T, seed, partitions): its serial-RNG kernel (a few dozen warps) runs on a side
-    // stream while split finding and binning use the rest of the GPU on the caller's stream.
+    // Bagging first, on a side stream forked from the caller's: the serial-RNG kernel runs under split finding and
+    // binning below.  (Letting it start before the caller's pending work — the window-feature kernel — was tried:
+    // its 111 KB CTAs then wait for free SMs and it finishes later.)
     const bool need_w = d_weights_in || !(T == 1 && p->subsampling_rate == 1.0);
+    SideStream side;                                     // declared before the buffers that are freed on it
     DevBuf<uint8_t> d_wbuf;
     DevBuf<int64_t> d_po;
     const uint8_t* d_w = d_weights_in;
-    SideStream side;
     if (need_w && !d_weights_in && n > 0) {
         HAR_CUDA(d_wbuf.alloc((size_t)T * n, s));
         d_w = d_wbuf.p;
@@ -733,12 +731,29 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         }
     }
 
+    // labels -> u8 (validated like Classifier.extractLabeledPoints); the verdict is read at the first sync below
+    DevBuf<uint8_t> d_lab; DevBuf<unsigned long long> d_bad;
+    static thread_local Pinned<unsigned long long> h_bad_pin;
+    HAR_CUDA(h_bad_pin.reserve(1));
+    HAR_CUDA(d_lab.alloc(std::max<int64_t>(n, 1), s)); HAR_CUDA(d_bad.alloc(1, s));
+    HAR_CUDA(cudaMemsetAsync(d_bad.p, 0xff, sizeof(unsigned long long), s));
+    if (n) { k_labels_to_u8<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(d_y, n, C, d_lab.p, d_bad.p); HAR_LAUNCH_CHECK(); }
+    h_bad_pin.p[0] = ~0ULL;
+    HAR_CUDA(cudaMemcpyAsync(h_bad_pin.p, d_bad.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+
     std::unique_ptr<har_forest> fo(new har_forest());
     fo->T = T; fo->C = C; fo->F = F; fo->max_bins = MB; fo->max_depth = p->max_depth;
     fo->thresholds.assign((size_t)F * MB, 0.0);
     fo->nsplits.assign(F, 0);
     if (int rc = find_splits_impl(d_X, n, F, ld, m, MB, p->seed, part_off, num_parts, dist, fo->thresholds.data(),
                                   fo->nsplits.data(), s)) return rc;
+    HAR_CUDA(cudaStreamSynchronize(s));
+    if (h_bad_pin.p[0] != ~0ULL) {
+        const unsigned long long h_bad = h_bad_pin.p[0];
+        double v = 0;
+        cudaMemcpy(&v, d_y + h_bad, sizeof(double), cudaMemcpyDeviceToHost);
+        return fail(HAR_E_INVALID, "Classifier given dataset with invalid label %g.  Labels must be integers in range [0, %d).", v, C);
+    }
     for (int f = 0; f < F; f++) if (m.arity[f] == 0) { m.num_splits[f] = fo->nsplits[f]; m.num_bins[f] = fo->nsplits[f] + 1; }
     if (int rc = finish_meta(m)) return rc;
     for (int f = 0; f < F; f++)
@@ -757,6 +772,11 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     const size_t perm_len = (size_t)T * std::max<int64_t>(n, 1);
     HAR_CUDA(perm0.alloc(perm_len, s)); HAR_CUDA(perm1.alloc(perm_len, s));
     std::vector<int32_t> root_cnt(T, (int32_t)n);
+    // the per-tree row counts come back through page-locked memory behind an event, so that the host can go on
+    // preparing (buffers of the level loop) while the bagging kernel still runs; wait_roots() is the sync point
+    static thread_local Pinned<int32_t> h_root_cnt;
+    struct EventHolder { cudaEvent_t ev = nullptr; ~EventHolder() { if (ev) cudaEventDestroy(ev); } } ev_root;
+    bool roots_pending = false;
     if (n) {
         if (need_w) {
             const int nchunks = (int)ceil_div(n, INIT_CHUNK);
@@ -764,8 +784,11 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             k_init_count<<<dim3(nchunks, T), 256, 0, s>>>(d_w, n, d_chunk.p, nchunks); HAR_LAUNCH_CHECK();
             k_init_scan<<<(unsigned)ceil_div(T, 4), 128, 0, s>>>(d_chunk.p, nchunks, T, d_cnt.p); HAR_LAUNCH_CHECK();
             k_init_scatter<<<dim3(nchunks, T), 256, 0, s>>>(d_w, n, d_chunk.p, nchunks, perm0.p); HAR_LAUNCH_CHECK();
-            HAR_CUDA(cudaMemcpyAsync(root_cnt.data(), d_cnt.p, sizeof(int32_t) * T, cudaMemcpyDeviceToHost, s));
-            HAR_CUDA(cudaStreamSynchronize(s));
+            HAR_CUDA(h_root_cnt.reserve(T));
+            HAR_CUDA(cudaMemcpyAsync(h_root_cnt.p, d_cnt.p, sizeof(int32_t) * T, cudaMemcpyDeviceToHost, s));
+            HAR_CUDA(cudaEventCreateWithFlags(&ev_root.ev, cudaEventDisableTiming));
+            HAR_CUDA(cudaEventRecord(ev_root.ev, s));
+            roots_pending = true;
         } else {
             k_iota<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(perm0.p, n); HAR_LAUNCH_CHECK();
         }
@@ -791,12 +814,13 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     // trees + node stack (RandomForest.run)
     std::vector<std::vector<LNode>> trees(T);
     std::vector<std::vector<uint32_t>> tree_stats(T);      // [node][C] class counts, kept out of the hot LNode
-    for (int t = 0; t < T; t++) {
-        LNode r; r.id = 1; r.start = 0; r.count = root_cnt[t]; r.buf = 0;
-        trees[t].reserve(256);
-        trees[t].push_back(r);
-        tree_stats[t].assign(C, 0);
-    }
+    auto wait_roots = [&]() -> int {
+        if (!roots_pending) return HAR_OK;
+        HAR_CUDA(cudaEventSynchronize(ev_root.ev));
+        std::copy(h_root_cnt.p, h_root_cnt.p + T, root_cnt.begin());
+        roots_pending = false;
+        return HAR_OK;
+    };
     JavaRand rng(p->seed);
 
     // batch buffers
@@ -1403,6 +1427,15 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         t_prep += ms_since(t_a);
         return dd_fetch_info(S, nb_next);
     };
+    if (int rc = wait_roots()) return rc;
+    if (!device_grow) {
+        for (int t = 0; t < T; t++) {
+            LNode r; r.id = 1; r.start = 0; r.count = root_cnt[t]; r.buf = 0;
+            trees[t].reserve(256);
+            trees[t].push_back(r);
+            tree_stats[t].assign(C, 0);
+        }
+    }
     if (device_grow) {
         for (int k = 0; k < num_sets; k++) if (int rc = dd_start(sets[k])) return rc;
         for (;;) {

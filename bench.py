@@ -147,6 +147,14 @@ class ClockSampler:
         self._thr = threading.Thread(target=self._run, daemon=True)
         self._thr.start()
 
+    def sample_now(self):
+        t0 = time.perf_counter()
+        try:
+            self._sample()
+        except Exception:
+            pass
+        self.query_ms = getattr(self, "query_ms", []) + [round(1e3 * (time.perf_counter() - t0), 3)]
+
     def _sample(self):
         if self._nvml is not None:
             n = self._nvml
@@ -182,7 +190,8 @@ class ClockSampler:
                 if mask & bit:
                     reasons.add(name)
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max((r[1] for r in self.rows), default=None),
-                "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self._nvml is not None else "nvidia-smi"}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self._nvml is not None else "nvidia-smi",
+                "query_ms": getattr(self, "query_ms", []), "sampled": "between steps, inside the timed region"}
 
 
 def measured_peaks():
@@ -265,15 +274,21 @@ def run_ours(args):
     core.profile(enable=True, reset=True)
     core.launch_count(reset=True)
     if rank == 0:
-        clocks.start()
+        pass                       # clocks are sampled inside the loop below
     rec = []
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     e0.record()
     marks[0].record()
+    sample_at = {args.steps // 2, args.steps - 1} if rank == 0 else set()
     for i in range(args.steps):
         device_step(rec)
+        if i in sample_at:
+            # NVML queries from a concurrent thread were seen to stall CUDA calls that create resources (one step of
+            # 260 ms instead of 22); the clocks are therefore read here, inside the timed region, right after a step
+            # (the GPU has not left its load state), and the time of the query counts as step time.
+            clocks.sample_now()
         marks[i + 1].record()
     e1.record()
     barrier()
