@@ -183,6 +183,45 @@ def test_sibling_subtraction_changes_nothing(monkeypatch):
     assert single.num_groups > 4 * small.num_groups and single.total_nodes == plain_small.total_nodes
 
 
+def test_device_grown_forest_equals_host_driven_fit(monkeypatch):
+    """All-features fits grow the trees on the device (node tables, pruning and predict tables built by kernels;
+    flat arrays read back on demand).  The result must equal the host-driven loop (HAR_FIT_DEVICE_GROW=0), also
+    when only a few parent counter slots are available (HAR_KEPT_SLOTS) and when levels span several device
+    batches; predictions made before the arrays are read back must equal those made after."""
+    from har_b200 import core
+    X, y, arity = synth_tree_data(15000, F=12, C=4, seed=23, n_cat_unordered=1, n_cat_ordered=1)
+    Xt, _, _ = synth_tree_data(4000, F=12, C=4, seed=24, n_cat_unordered=1, n_cat_ordered=1)
+    kw = dict(arity=arity, num_classes=4, num_trees=7, max_depth=9, feature_subset="all", seed=11, max_bins=32)
+    g = core.fit_forest(X, y, **kw)
+    before = [t.cpu().numpy() for t in g.predict(Xt, is_forest=True)]      # tables written by the fit
+    as_tree = [t.cpu().numpy() for t in g.predict(Xt, is_forest=False)]    # leaf vectors rebuilt for the other mode
+    n_dev = g.total_nodes                                                  # counted on the device
+    assert len(g.feature) == n_dev                                         # read-back of the node pools
+    after = [t.cpu().numpy() for t in g.predict(Xt, is_forest=True)]
+    for a, b in zip(before, after):
+        assert np.array_equal(_bits(a), _bits(b))
+    o = orc.fit_forest(X, y, **kw)
+    assert_forest_equal(o, g)
+    ro, po_, pr = orc.predict(o, Xt, is_forest=True)
+    assert np.array_equal(_bits(before[0]), _bits(ro)) and np.array_equal(before[2], pr)
+    monkeypatch.setenv("HAR_KEPT_SLOTS", "5")
+    monkeypatch.setenv("HAR_HIST_BUDGET_WORDS", "60000")
+    few = core.fit_forest(X, y, **kw)
+    assert few.num_batches > 2 * g.num_batches
+    assert_forest_equal(g, few)
+    monkeypatch.delenv("HAR_KEPT_SLOTS"); monkeypatch.delenv("HAR_HIST_BUDGET_WORDS")
+    monkeypatch.setenv("HAR_FIT_DEVICE_GROW", "0")
+    host = core.fit_forest(X, y, **kw)
+    assert_forest_equal(g, host)
+    assert host.num_groups == g.num_groups == o.num_groups
+    hp = [t.cpu().numpy() for t in host.predict(Xt, is_forest=True)]
+    for a, b in zip(before, hp):
+        assert np.array_equal(_bits(a), _bits(b))
+    ht = [t.cpu().numpy() for t in host.predict(Xt, is_forest=False)]     # tables built on the host from the flat arrays
+    for a, b in zip(as_tree, ht):
+        assert np.array_equal(_bits(a), _bits(b))
+
+
 def test_count_division_is_the_ieee_division():
     """k_best_split divides class counts with the fast path of __ddiv_rn spelled out (no range checks, no slow
     path for zero numerators); over 2^28 random and edge operand pairs of its domain it must equal __ddiv_rn
