@@ -64,6 +64,41 @@ HAR_API int har_stream_synchronize(har_stream_t stream) {
     return HAR_OK;
 }
 
+// ---- per-thread device scratch arena (see har_common.cuh) ------------------------------------------------------
+namespace har {
+Arena& arena() { static thread_local Arena a; return a; }
+ArenaScope::ArenaScope() {
+    Arena& a = arena();
+    if (a.active) return;                              // nested scope: the outer one owns the arena
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return;
+    if (a.base && a.dev != dev) { cudaFree(a.base); a.base = nullptr; a.cap = 0; }
+    a.dev = dev; a.off = 0; a.need = 0; a.active = true;
+    owner = true;
+}
+ArenaScope::~ArenaScope() {
+    if (!owner) return;
+    Arena& a = arena();
+    a.active = false;
+    if (a.need > a.cap) {                              // grow for the next call; everything of this call has been freed
+        if (a.base) cudaFree(a.base);
+        a.base = nullptr; a.cap = 0;
+        const size_t want = a.need + a.need / 16 + (1 << 20);
+        void* q = nullptr;
+        if (cudaMalloc(&q, want) == cudaSuccess) { a.base = (char*)q; a.cap = want; }
+        else cudaGetLastError();                       // no slab: the stream-ordered allocator keeps being used
+    }
+}
+}  // namespace har
+
+// frees the calling thread's device scratch arena (it is otherwise kept between fits)
+HAR_API void har_scratch_release(void) {
+    har::Arena& a = har::arena();
+    if (a.active) return;
+    if (a.base) cudaFree(a.base);
+    a.base = nullptr; a.cap = 0;
+}
+
 // ---- persistent host thread pool behind parallel_for ---------------------------------------------------
 namespace har {
 namespace {

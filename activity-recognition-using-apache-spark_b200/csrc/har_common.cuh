@@ -57,28 +57,56 @@ void prof_resolve();
 void pool_setup();
 
 // Stream-ordered scratch buffer (cudaMallocAsync); freed on the same stream.
+// Per-thread device scratch arena.  A fit allocates tens of buffers, some of them gigabytes; through the
+// stream-ordered allocator that cost 20 ms per fit at 1e9 samples and, now and then, 100-700 ms (the pool mapping
+// fresh memory).  While an ArenaScope is active, DevBuf carves its memory from one slab that is kept between calls
+// (bump pointer, nothing is recycled inside a scope); the slab is regrown at the end of a scope that needed more.
+// Buffers that outlive the call ask for persistent memory and bypass the arena.  har_scratch_release() frees it.
+struct Arena { char* base = nullptr; size_t cap = 0, off = 0, need = 0; int dev = -1; bool active = false; };
+Arena& arena();
+struct ArenaScope {
+    bool owner = false;
+    ArenaScope();
+    ~ArenaScope();
+};
+
 template <typename T>
 struct DevBuf {
     T* p = nullptr;
     size_t n = 0;
     cudaStream_t s = nullptr;
+    bool from_arena = false;
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
     ~DevBuf() { release(); }
-    cudaError_t alloc(size_t count, cudaStream_t stream) {
+    cudaError_t alloc(size_t count, cudaStream_t stream, bool persistent = false) {
         release();
         s = stream;
         n = count;
         if (count == 0) return cudaSuccess;
+        Arena& a = arena();
+        if (a.active && !persistent) {
+            const size_t bytes = (count * sizeof(T) + 255) & ~(size_t)255;
+            a.need += bytes;
+            if (a.off + bytes <= a.cap) {
+                p = reinterpret_cast<T*>(a.base + a.off);
+                a.off += bytes;
+                from_arena = true;
+                return cudaSuccess;
+            }
+        }
         pool_setup();
         return cudaMallocAsync((void**)&p, count * sizeof(T), stream);
     }
     void release() {
-        if (p) cudaFreeAsync(p, s);
+        if (p && !from_arena) cudaFreeAsync(p, s);
         p = nullptr;
         n = 0;
+        from_arena = false;
     }
+    void swap(DevBuf& o) { std::swap(p, o.p); std::swap(n, o.n); std::swap(s, o.s); std::swap(from_arena, o.from_arena); }
+    T* detach() { T* q = p; p = nullptr; n = 0; from_arena = false; return q; }   // caller takes ownership (persistent buffers only)
 };
 
 inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -674,6 +674,7 @@ HAR_API int har_node_histogram(const uint8_t* d_bins, int64_t ldb, const uint8_t
 HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, const double* d_y, const int32_t* arity,
                            const int64_t* part_off_in, int32_t num_parts, const har_fit_params* p, const har_dist* dist,
                            const uint8_t* d_weights_in, har_stream_t stream, har_forest_t** out) {
+    ArenaScope scratch_scope;                            // device scratch of this call comes from the thread's arena
     // host threads for the driver-side work: the ranks of a node share its cores
     host_threads_set_ranks(dist ? dist->world_size : 1);
     if (!out || !p) return fail(HAR_E_INVALID, "har_forest_fit: NULL params / out");
@@ -703,6 +704,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     auto ms_since = [&](std::chrono::steady_clock::time_point a) { return std::chrono::duration<double, std::milli>(now() - a).count(); };
     double t_prep = 0, t_wait = 0, t_post = 0;
     auto t_begin = now();
+    std::string setup_marks;                             // HAR_FIT_TRACE: host time at the setup milestones
+    auto mark = [&](const char* what) { if (trace) { char b[64]; snprintf(b, sizeof b, " %s %.2f", what, ms_since(t_begin)); setup_marks += b; } };
 
     Meta m;
     if (int rc = build_meta(m, F, C, n_global, MB, arity)) return rc;
@@ -741,12 +744,14 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     h_bad_pin.p[0] = ~0ULL;
     HAR_CUDA(cudaMemcpyAsync(h_bad_pin.p, d_bad.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
 
+    mark("bag+labels launched");
     std::unique_ptr<har_forest> fo(new har_forest());
     fo->T = T; fo->C = C; fo->F = F; fo->max_bins = MB; fo->max_depth = p->max_depth;
     fo->thresholds.assign((size_t)F * MB, 0.0);
     fo->nsplits.assign(F, 0);
     if (int rc = find_splits_impl(d_X, n, F, ld, m, MB, p->seed, part_off, num_parts, dist, fo->thresholds.data(),
                                   fo->nsplits.data(), s)) return rc;
+    mark("find_splits");
     HAR_CUDA(cudaStreamSynchronize(s));
     if (h_bad_pin.p[0] != ~0ULL) {
         const unsigned long long h_bad = h_bad_pin.p[0];
@@ -765,6 +770,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     if (ldb != F) HAR_CUDA(cudaMemsetAsync(d_bins.p, 0, (size_t)std::max<int64_t>(n, 1) * ldb, s));   // zero padding bytes
     if (int rc = bin_features_impl(d_X, n, F, ld, arity, fo->thresholds.data(), fo->nsplits.data(), MB, d_bins.p, ldb, s)) return rc;
 
+    mark("binned");
     HAR_CUDA(side.join(s));                              // weights are needed from here on
 
     // row permutations
@@ -794,6 +800,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         }
     }
 
+    mark("perm init launched");
     // device-side metadata
     DevBuf<uint8_t> d_kind; DevBuf<int32_t> d_nsplits, d_hbins, d_loff_all;
     HAR_CUDA(d_kind.alloc(F, s)); HAR_CUDA(d_nsplits.alloc(F, s)); HAR_CUDA(d_hbins.alloc(F, s));
@@ -873,7 +880,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         DevBuf<NodeDesc> d_nodes;
         DevBuf<NodeResult> d_res;
         DevBuf<int32_t> d_item_off, d_hitem_off, d_chunk_left, d_flist_all;
-        size_t cap_nodes = 0, cap_hist = 0, cap_items = 0, cap_sub = 0;
+        DevBuf<uint32_t> d_lbits;                            // routing bits of the rows being partitioned
+        size_t cap_nodes = 0, cap_hist = 0, cap_items = 0, cap_sub = 0, cap_lbits = 0;
         HistStore store;
         int64_t batch_stamp = 0;
         // device-driven growth (all-features fits): node tables of two consecutive levels, per-batch launch data,
@@ -939,6 +947,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             HAR_CUDA(S.d_hist.alloc(S.cap_hist, s));
             S.cap_items = (size_t)(ceil_div(n * Ts, 256) + per_batch + 1);
             HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, s));
+            S.cap_lbits = (size_t)((n * Ts + per_batch * 4096) / 32 + 1024);   // items x chunk_rows <= rows + nodes x chunk_rows
+            HAR_CUDA(S.d_lbits.alloc(S.cap_lbits, s));
             int64_t kslots = 0;
             if (subtract && p->max_depth >= 2) kslots = std::min(kept_cap_slots, std::min(lvl, Ts << std::min(p->max_depth - 2, 22)));
             for (int w = 0; w < 2; w++) {
@@ -948,7 +958,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             int64_t pool = std::min<int64_t>(Ts << std::min(p->max_depth + 1, 23), 2 * rows_g * Ts);
             pool = std::max<int64_t>(Ts, std::min<int64_t>(pool, 4 << 20));
             S.cap_pool = (size_t)pool;
-            HAR_CUDA(S.pool_res.alloc(pool, s)); HAR_CUDA(S.pool_stats.alloc((size_t)pool * 3 * C, s)); HAR_CUDA(S.pool_meta.alloc(pool, s));
+            HAR_CUDA(S.pool_res.alloc(pool, s, true)); HAR_CUDA(S.pool_stats.alloc((size_t)pool * 3 * C, s, true)); HAR_CUDA(S.pool_meta.alloc(pool, s, true));   // move into the forest
         }
         if (own_streams) { HAR_CUDA(set_side[k].fork(s)); sets[k].st = set_side[k].s; }
         sets[k].store.slot_words = (size_t)full_len + C;
@@ -957,8 +967,10 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     for (int t = 0; t < T; t++) sets[t % num_sets].stack.push_back({t, 0});
     int64_t groups_run = 0;
 
+    mark("buffers");
     if (trace) cudaStreamSynchronize(s);
     const double t_setup = ms_since(t_begin);
+    if (trace) fprintf(stderr, "[har_forest_fit]   setup marks (ms):%s | synced %.2f\n", setup_marks.c_str(), t_setup);
 
     // ---- selectNodesToSplit ----
     auto select_group = [&](FitSet& S) {
@@ -1079,6 +1091,10 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             }
             if (need_hist > S.cap_hist) { S.cap_hist = need_hist + need_hist / 4; HAR_CUDA(S.d_hist.alloc(S.cap_hist, S.st)); }
             if ((size_t)items + 1 > S.cap_items) { S.cap_items = (size_t)items * 2 + 1; HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, S.st)); }
+            {
+                const size_t lw = (size_t)items * (size_t)(chunk_rows >> 5) + 1;
+                if (lw > S.cap_lbits) { S.cap_lbits = lw + lw / 2; HAR_CUDA(S.d_lbits.alloc(S.cap_lbits, S.st)); }
+            }
             if (subsample && (size_t)ng * (K + 1) * 2 > S.cap_sub) {
                 S.cap_sub = (size_t)ng * (K + 1) * 4;
                 HAR_CUDA(S.d_flist_all.alloc(S.cap_sub, S.st));
@@ -1124,14 +1140,14 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             if (!all_last_level && items > 0) {
                 prof_begin(S.st);
                 k_part_count<<<(unsigned)items, HIST_THREADS, 0, S.st>>>(S.d_nodes.p, S.d_item_off.p, ng, chunk_rows, S.d_res.p, d_bins.p, ldb, n,
-                                                                      perm0.p, perm1.p, S.d_chunk_left.p);
+                                                                      perm0.p, perm1.p, S.d_chunk_left.p, S.d_lbits.p);
                 HAR_LAUNCH_CHECK();
                 prof_end(PROF_PART_COUNT, S.st, (double)rows_total);
                 k_part_scan<<<(unsigned)ceil_div(ng, 4), 128, 0, S.st>>>(S.d_item_off.p, ng, S.d_res.p, S.d_chunk_left.p);
                 HAR_LAUNCH_CHECK();
                 prof_begin(S.st);
                 k_part_scatter<<<(unsigned)items, HIST_THREADS, 0, S.st>>>(S.d_nodes.p, S.d_item_off.p, ng, chunk_rows, S.d_res.p, d_bins.p, ldb, n,
-                                                                        perm0.p, perm1.p, S.d_chunk_left.p);
+                                                                        perm0.p, perm1.p, S.d_chunk_left.p, S.d_lbits.p);
                 HAR_LAUNCH_CHECK();
                 prof_end(PROF_PART_SCATTER, S.st, (double)rows_total);
             }
@@ -1335,15 +1351,13 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         if ((size_t)(base + ncur) > S.cap_pool) {                       // grow the pool of finished nodes, keeping its content
             const size_t ncap = std::max<size_t>((size_t)(base + ncur) * 2, 4096);
             DevBuf<NodeResult> nr_; DevBuf<uint32_t> ns_; DevBuf<PoolMeta> nm_;
-            HAR_CUDA(nr_.alloc(ncap, S.st)); HAR_CUDA(ns_.alloc(ncap * 3 * C, S.st)); HAR_CUDA(nm_.alloc(ncap, S.st));
+            HAR_CUDA(nr_.alloc(ncap, S.st, true)); HAR_CUDA(ns_.alloc(ncap * 3 * C, S.st, true)); HAR_CUDA(nm_.alloc(ncap, S.st, true));
             if (base > 0) {
                 HAR_CUDA(cudaMemcpyAsync(nr_.p, S.pool_res.p, sizeof(NodeResult) * base, cudaMemcpyDeviceToDevice, S.st));
                 HAR_CUDA(cudaMemcpyAsync(ns_.p, S.pool_stats.p, sizeof(uint32_t) * base * 3 * C, cudaMemcpyDeviceToDevice, S.st));
                 HAR_CUDA(cudaMemcpyAsync(nm_.p, S.pool_meta.p, sizeof(PoolMeta) * base, cudaMemcpyDeviceToDevice, S.st));
             }
-            std::swap(S.pool_res.p, nr_.p); std::swap(S.pool_res.n, nr_.n); std::swap(S.pool_res.s, nr_.s);
-            std::swap(S.pool_stats.p, ns_.p); std::swap(S.pool_stats.n, ns_.n); std::swap(S.pool_stats.s, ns_.s);
-            std::swap(S.pool_meta.p, nm_.p); std::swap(S.pool_meta.n, nm_.n); std::swap(S.pool_meta.s, nm_.s);
+            S.pool_res.swap(nr_); S.pool_stats.swap(ns_); S.pool_meta.swap(nm_);
             S.cap_pool = ncap;
         }
         const bool last_level = L + 1 >= p->max_depth;                  // no child of this level can be split
@@ -1357,6 +1371,10 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             const size_t need_hist = reduce_words + (size_t)bi.n_derived * full_len;
             if (need_hist > S.cap_hist) { S.cap_hist = need_hist + need_hist / 4; HAR_CUDA(S.d_hist.alloc(S.cap_hist, S.st)); }
             if ((size_t)bi.items + 1 > S.cap_items) { S.cap_items = (size_t)bi.items * 2 + 1; HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, S.st)); }
+            {
+                const size_t lw = (size_t)bi.items * (size_t)(bi.chunk_rows >> 5) + 1;
+                if (lw > S.cap_lbits) { S.cap_lbits = lw + lw / 2; HAR_CUDA(S.d_lbits.alloc(S.cap_lbits, S.st)); }
+            }
             const NodeDesc* nodes = S.lv_nodes[cur].p + b * batch_cap;
             const int32_t* io = S.lv_item_off[cur].p + b * (batch_cap + 1);
             const int32_t* ho = S.lv_hitem_off[cur].p + b * (batch_cap + 1);
@@ -1389,14 +1407,14 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 if (bi.items > 0) {
                     prof_begin(S.st);
                     k_part_count<<<(unsigned)bi.items, HIST_THREADS, 0, S.st>>>(nodes, io, ng, bi.chunk_rows, res, d_bins.p, ldb, n,
-                                                                               perm0.p, perm1.p, S.d_chunk_left.p);
+                                                                               perm0.p, perm1.p, S.d_chunk_left.p, S.d_lbits.p);
                     HAR_LAUNCH_CHECK();
                     prof_end(PROF_PART_COUNT, S.st, (double)bi.rows_total);
                     k_part_scan<<<(unsigned)ceil_div(ng, 4), 128, 0, S.st>>>(io, ng, res, S.d_chunk_left.p);
                     HAR_LAUNCH_CHECK();
                     prof_begin(S.st);
                     k_part_scatter<<<(unsigned)bi.items, HIST_THREADS, 0, S.st>>>(nodes, io, ng, bi.chunk_rows, res, d_bins.p, ldb, n,
-                                                                                 perm0.p, perm1.p, S.d_chunk_left.p);
+                                                                                 perm0.p, perm1.p, S.d_chunk_left.p, S.d_lbits.p);
                     HAR_LAUNCH_CHECK();
                     prof_end(PROF_PART_SCATTER, S.st, (double)bi.rows_total);
                 }
@@ -1536,8 +1554,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             FitSet& S = sets[k];
             LazyPools::SetPool& sp = lazy->set[k];
             sp.my_trees = S.my_trees; sp.N = S.pool_used;
-            sp.res = S.pool_res.p; sp.stats = S.pool_stats.p; sp.meta = S.pool_meta.p;
-            S.pool_res.p = nullptr; S.pool_stats.p = nullptr; S.pool_meta.p = nullptr;
+            sp.res = S.pool_res.detach(); sp.stats = S.pool_stats.detach(); sp.meta = S.pool_meta.detach();
         }
         const int64_t cost = (int64_t)C * total_bins_all * 8, max_mem = p->max_memory_bytes;
         fo->count_groups = [lazy, cost, max_mem]() -> int64_t {

@@ -58,6 +58,7 @@ _SIGS = {
     "har_device_count": (C.c_int, [C.POINTER(C.c_int32)]),
     "har_set_device": (C.c_int, [C.c_int32]),
     "har_stream_synchronize": (C.c_int, [C.c_void_p]),
+    "har_scratch_release": (None, []),
     "har_debug_launch_count": (C.c_longlong, [C.c_int]),
     "har_debug_comm_stats": (None, [C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), C.POINTER(C.c_int), C.c_int]),
     "har_debug_div_check": (C.c_int, [C.c_longlong, C.c_ulonglong, C.POINTER(C.c_ulonglong), C.c_void_p]),

@@ -51,6 +51,12 @@ int har_device_count(int32_t* count);
 int har_set_device(int32_t device);
 int har_stream_synchronize(har_stream_t stream);
 
+/* har_forest_fit keeps its device scratch (row permutations, counters, node tables: ~3 GB at 5e5 rows x 100 trees,
+ * ~14 GB at 5e6 rows) in a per-thread arena between calls, because re-allocating gigabytes per fit through the
+ * stream-ordered allocator cost tens to hundreds of milliseconds.  This releases the calling thread's arena.
+ * No reference counterpart (Spark's executors keep their own caches). */
+void har_scratch_release(void);
+
 /* ------------------------------------------------------------------------------------------------
  * (1)+(2) WISDM window transform.  No reference code exists for this stage: the
  * reference only ships its OUTPUT, Main/wisdm_main_ver_0.0/data/wisdm_data.csv (schema :1), read at
