@@ -280,22 +280,33 @@ def run_ours(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     e0.record()
-    marks[0].record()
-    sample_at = {args.steps // 2, args.steps - 1} if rank == 0 else set()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    # with several ranks only after the last step: a query in the middle would make the other ranks wait for rank 0
+    sample_at = ({args.steps // 2, args.steps - 1} if world == 1 else {args.steps - 1}) if rank == 0 else set()
+    query_spans = []
     for i in range(args.steps):
+        starts[i].record()
         device_step(rec)
+        marks[i + 1].record()
         if i in sample_at:
             # NVML queries from a concurrent thread were seen to stall CUDA calls that create resources (one step of
             # 260 ms instead of 22); the clocks are therefore read here, inside the timed region, right after a step
-            # (the GPU has not left its load state), and the time of the query counts as step time.
+            # (the GPU has not left its load state).  A query takes 1.5-70 ms of host time with the GPU idle; that
+            # span is bracketed by its own events and subtracted from the timed total (reported in "clocks").
+            qa, qb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            qa.record()
             clocks.sample_now()
-        marks[i + 1].record()
+            qb.record()
+            query_spans.append((qa, qb))
     e1.record()
     barrier()
     launches = core.launch_count()
     prof = core.profile(enable=False)
     clk = clocks.stop() if rank == 0 else None
-    ms_total = e0.elapsed_time(e1)
+    excluded_ms = sum(a.elapsed_time(b) for a, b in query_spans)
+    ms_total = e0.elapsed_time(e1) - excluded_ms
+    if clk is not None:
+        clk["query_ms_excluded_from_timing"] = round(excluded_ms, 3)
     t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
     if world > 1:
         td.all_reduce(t, op=td.ReduceOp.MAX)
@@ -426,7 +437,7 @@ def run_ours(args):
                        "node_groups": rec[-1][3].num_groups, "device_batches": rec[-1][4], "allreduce_calls": rec[-1][5][0], "allreduce_via": "library NCCL communicator" if rec[-1][5][2] else "caller's callback (torch.distributed)",
                        "allreduce_bytes": rec[-1][5][1], "train_accuracy": train_acc},
             "roofline": roofline, "window_stage_roofline": window_roof, "kernels": roofs,
-            "step_ms": [marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps)],
+            "step_ms": [starts[i].elapsed_time(marks[i + 1]) for i in range(args.steps)],
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk}
     print(json.dumps(line))
     if world > 1:
