@@ -42,21 +42,40 @@ k_predict(const PNode* __restrict__ nodes, const int64_t* __restrict__ roots, in
     if (i >= n) return;
     const double* x = STAGE ? xs + (size_t)threadIdx.x * fstride : X + i * ld;
     for (int c = 0; c < C; c++) acc[c * PRED_THREADS + threadIdx.x] = 0.0;
-    for (int t = 0; t < T; t++) {
-        int64_t k = roots[t];
-        PNode nd = nodes[k];
-        while (nd.feature >= 0) {
-            const double v = x[nd.feature & P_FMASK];
-            bool go_left;
-            if (nd.feature & P_CAT) {
-                const bool in_dom = v >= 0.0 && v < 64.0 && v == floor(v);
-                go_left = in_dom ? (bool)((nd.mask >> (int)v) & 1ULL) : (bool)(nd.feature & P_DEFLEFT);
-            } else {
-                go_left = v <= nd.thr;
-            }
-            k = nd.left + (go_left ? 0 : 1);
-            nd = nodes[k];
+    // Four trees are walked at once: a walk is a chain of dependent node loads (L2 latency each), so interleaving
+    // independent walks multiplies the loads in flight per thread.  The leaf vectors are then added in tree order,
+    // which keeps MLlib's sequence of fp64 additions.
+    auto step = [&](PNode& nd) {
+        const double v = x[nd.feature & P_FMASK];
+        bool go_left;
+        if (nd.feature & P_CAT) {
+            const bool in_dom = v >= 0.0 && v < 64.0 && v == floor(v);
+            go_left = in_dom ? (bool)((nd.mask >> (int)v) & 1ULL) : (bool)(nd.feature & P_DEFLEFT);
+        } else {
+            go_left = v <= nd.thr;
         }
+        nd = nodes[nd.left + (go_left ? 0 : 1)];
+    };
+    int t = 0;
+    for (; t + 4 <= T; t += 4) {
+        PNode n0 = nodes[roots[t]], n1 = nodes[roots[t + 1]], n2 = nodes[roots[t + 2]], n3 = nodes[roots[t + 3]];
+        while ((n0.feature >= 0) | (n1.feature >= 0) | (n2.feature >= 0) | (n3.feature >= 0)) {
+            if (n0.feature >= 0) step(n0);
+            if (n1.feature >= 0) step(n1);
+            if (n2.feature >= 0) step(n2);
+            if (n3.feature >= 0) step(n3);
+        }
+        const double* l0 = leaf + (int64_t)n0.left * C; const double* l1 = leaf + (int64_t)n1.left * C;
+        const double* l2 = leaf + (int64_t)n2.left * C; const double* l3 = leaf + (int64_t)n3.left * C;
+        for (int c = 0; c < C; c++) {
+            double a = acc[c * PRED_THREADS + threadIdx.x];
+            a += l0[c]; a += l1[c]; a += l2[c]; a += l3[c];
+            acc[c * PRED_THREADS + threadIdx.x] = a;
+        }
+    }
+    for (; t < T; t++) {
+        PNode nd = nodes[roots[t]];
+        while (nd.feature >= 0) step(nd);
         const double* lv = leaf + (int64_t)nd.left * C;
         for (int c = 0; c < C; c++) acc[c * PRED_THREADS + threadIdx.x] += lv[c];
     }
