@@ -95,6 +95,9 @@ _SIGS = {
     "har_forest_free": (None, [C.c_void_p]),
     "har_forest_predict": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_void_p]),
+    "har_parse_wisdm_raw": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_char_p), C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                      C.c_void_p]),
     "har_csr_to_dense": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int64,
                                    C.c_void_p]),
 }

@@ -362,6 +362,36 @@ def fit_forest(X, y, arity=None, num_classes=None, num_trees=1, max_depth=5, max
     return fo
 
 
+WISDM_ACTIVITIES = ("Walking", "Jogging", "Upstairs", "Downstairs", "Sitting", "Standing")
+
+
+def parse_wisdm_raw(text, activities=WISDM_ACTIVITIES):
+    """Raw WISDM records ("user,activity,timestamp,x,y,z;") -> (user i32, activity i32, ts i64, x, y, z f64) CUDA
+    tensors plus the number of dropped records.  `text`: bytes / bytearray / uint8 array / CUDA uint8 tensor."""
+    require_cuda()
+    if isinstance(text, torch.Tensor):
+        t = text.to(device="cuda", dtype=torch.uint8).contiguous()
+    else:
+        a = np.frombuffer(bytes(text), dtype=np.uint8) if not isinstance(text, np.ndarray) else np.ascontiguousarray(text, np.uint8)
+        COUNTERS["h2d_bytes"] += a.nbytes
+        t = torch.from_numpy(a.copy()).cuda() if a.size else torch.empty(0, dtype=torch.uint8, device="cuda")
+    names = (C.c_char_p * len(activities))(*[s.encode() for s in activities])
+    nrec, ndrop = C.c_int64(), C.c_int64()
+    # sizing call, then the columns
+    rc = N.lib().har_parse_wisdm_raw(ptr(t), t.numel(), names, len(activities), 0, None, None, None, None, None, None,
+                                     C.byref(nrec), C.byref(ndrop), stream())
+    if rc != 0 and nrec.value == 0:
+        N.check(rc)
+    n = nrec.value
+    user = torch.empty(n, dtype=torch.int32, device="cuda"); act = torch.empty_like(user)
+    ts = torch.empty(n, dtype=torch.int64, device="cuda")
+    x = torch.empty(n, dtype=torch.float64, device="cuda"); y = torch.empty_like(x); z = torch.empty_like(x)
+    if n:
+        N.check(N.lib().har_parse_wisdm_raw(ptr(t), t.numel(), names, len(activities), n, ptr(user), ptr(act), ptr(ts), ptr(x),
+                                            ptr(y), ptr(z), C.byref(nrec), C.byref(ndrop), stream()))
+    return (user, act, ts, x, y, z), int(ndrop.value)
+
+
 def csr_to_dense(indptr, indices, values, n, F):
     require_cuda()
     ip, ix, vv = dev(indptr, np.int64), dev(indices, np.int32), dev(values, np.float64)

@@ -87,3 +87,21 @@ class WisdmWindowFeaturizer(Transformer):
 
 
 _make_accessors(WisdmWindowFeaturizer, _NAMES)
+
+
+def read_wisdm_raw(path_or_bytes, activities=core.WISDM_ACTIVITIES):
+    """Raw WISDM release text (records "user,activity,timestamp,x,y,z;") -> DataFrame(user, activity, timestamp, x, y,
+    z) whose columns stay on the GPU until read; activity is the index into `activities`.  Broken records are
+    dropped (their count is in df.dropped_records).  Feed the result to WisdmWindowFeaturizer.transform."""
+    if isinstance(path_or_bytes, (bytes, bytearray, memoryview)):
+        data = bytes(path_or_bytes)
+    else:
+        with open(path_or_bytes, "rb") as fh:
+            data = fh.read()
+    (user, act, ts, x, y, z), dropped = core.parse_wisdm_raw(data, activities)
+    cols = {"user": DeviceColumn(user, np.int32), "activity": DeviceColumn(act, np.int32), "timestamp": DeviceColumn(ts, np.int64),
+            "x": DeviceColumn(x, np.float64), "y": DeviceColumn(y, np.float64), "z": DeviceColumn(z, np.float64)}
+    types = {"user": "int", "activity": "int", "timestamp": "bigint", "x": "double", "y": "double", "z": "double"}
+    df = DataFrame(cols, types)
+    df.dropped_records = dropped
+    return df

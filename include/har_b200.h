@@ -229,6 +229,21 @@ int har_forest_predict(const har_forest_t* f, const double* d_X, int64_t n, int6
                        int32_t is_forest, double* d_raw, double* d_prob, double* d_pred,
                        har_stream_t stream);
 
+/* f4 — raw WISDM text ingest (no call site in Main/main.py, which starts from the already
+ * transformed wisdm_data.csv at main.py:18-26 — this is the step ahead of a1/a2 for the raw release
+ * WISDM_ar_v1.1_raw.txt).  d_text: device bytes, records "user,activity,timestamp,x,y,z;" (one or several per line).
+ * Blanks around records and fields are ignored, empty records vanish, a record that does not have six non-empty
+ * fields of the right kinds (int user, one of `activity_names` -> its index, int64 timestamp, three decimals) is
+ * dropped and counted in *num_dropped; text after the last ';' is one more record.  Decimals are converted exactly (what
+ * strtod / Double.parseDouble return) when they have <= 15 significant digits and a decimal exponent in [-22, 22];
+ * anything longer fails with HAR_E_UNSUPPORTED instead of being approximated.  Outputs: the six columns of
+ * har_window_segments / har_window_features, *num_records of them (HAR_E_INVALID if > capacity; call with
+ * capacity 0 and NULL columns to size).  Synchronises. */
+int har_parse_wisdm_raw(const char* d_text, int64_t nbytes, const char* const* activity_names,
+                        int32_t num_names, int64_t capacity, int32_t* d_user, int32_t* d_activity,
+                        int64_t* d_ts, double* d_x, double* d_y, double* d_z, int64_t* num_records,
+                        int64_t* num_dropped, har_stream_t stream);
+
 /* CSR -> dense row-major f64 (the reference's `features` column is a 3100-d SparseVector,
  * result.txt:110).  d_out [n][ld] is fully overwritten.  Asynchronous. */
 int har_csr_to_dense(const int64_t* d_indptr, const int32_t* d_indices, const double* d_values,

@@ -1056,3 +1056,78 @@ ORC_API int orc_num_threads(void) {
     return 1;
 #endif
 }
+
+/* ---- raw WISDM text ingest (no reference code: the rules are those of
+ * include/har_b200.h har_parse_wisdm_raw, restated with strtod / strtoll).  Returns the number of valid records
+ * (written up to `capacity`), *dropped = malformed records. ------------------------------------------------------ */
+static int orc_blank(unsigned char c) { return c == ' ' || c == '\t' || c == '\r' || c == '\n'; }
+
+static int orc_field_number(const char* p, const char* q, int want_int, long long* iv, double* dv) {
+    char buf[64];
+    size_t L = (size_t)(q - p);
+    if (L == 0 || L >= sizeof buf) return 1;
+    for (size_t i = 0; i < L; i++) {
+        char c = p[i];
+        int ok = (c >= '0' && c <= '9') || c == '-' || c == '+' || (!want_int && (c == '.' || c == 'e' || c == 'E'));
+        if (!ok) return 1;
+    }
+    memcpy(buf, p, L); buf[L] = 0;
+    char* end = NULL;
+    if (want_int) {
+        size_t digits = L - ((buf[0] == '-' || buf[0] == '+') ? 1 : 0);
+        if (digits == 0 || digits > 18) return 1;
+        *iv = strtoll(buf, &end, 10);
+    } else *dv = strtod(buf, &end);
+    return (end == buf + L) ? 0 : 1;
+}
+
+ORC_API int64_t orc_parse_wisdm_raw(const char* text, int64_t nbytes, const char* const* names, int32_t num_names, int64_t capacity,
+                            int32_t* user, int32_t* act, int64_t* ts, double* x, double* y, double* z, int64_t* dropped) {
+    int64_t nvalid = 0, ndrop = 0, a = 0;
+    for (int64_t i = 0; i <= nbytes; i++) {
+        if (i < nbytes && text[i] != ';') continue;
+        int64_t s = a, e = i;
+        a = i + 1;
+        while (s < e && orc_blank((unsigned char)text[s])) s++;
+        while (e > s && orc_blank((unsigned char)text[e - 1])) e--;
+        if (s >= e) continue;                                  /* empty record (or blank tail) */
+        const char* f0[6]; const char* f1[6];
+        int nf = 0, bad = 0;
+        const char* st = text + s;
+        for (const char* p = text + s;; p++) {
+            if (p == text + e || *p == ',') {
+                if (nf == 6) { bad = 1; break; }
+                f0[nf] = st; f1[nf] = p; nf++;
+                if (p == text + e) break;
+                st = p + 1;
+            }
+        }
+        if (bad || nf != 6) { ndrop++; continue; }
+        for (int k = 0; k < 6 && !bad; k++) {
+            while (f0[k] < f1[k] && orc_blank((unsigned char)*f0[k])) f0[k]++;
+            while (f1[k] > f0[k] && orc_blank((unsigned char)*(f1[k] - 1))) f1[k]--;
+            if (f0[k] >= f1[k]) bad = 1;
+        }
+        long long u = 0, t = 0;
+        double v[3] = {0, 0, 0};
+        int ai = -1;
+        if (!bad) bad = orc_field_number(f0[0], f1[0], 1, &u, NULL) || u < -2147483647LL || u > 2147483647LL;
+        if (!bad) {
+            size_t L = (size_t)(f1[1] - f0[1]);
+            for (int k = 0; k < num_names && ai < 0; k++) if (strlen(names[k]) == L && memcmp(names[k], f0[1], L) == 0) ai = k;
+            bad = ai < 0;
+        }
+        if (!bad) bad = orc_field_number(f0[2], f1[2], 1, &t, NULL);
+        for (int k = 0; k < 3 && !bad; k++) {
+            /* a decimal needs at least one digit in its mantissa ("." or "-" alone are malformed) */
+            int has_digit = 0;
+            for (const char* p = f0[3 + k]; p < f1[3 + k] && *p != 'e' && *p != 'E'; p++) has_digit |= (*p >= '0' && *p <= '9');
+            bad = !has_digit || orc_field_number(f0[3 + k], f1[3 + k], 0, NULL, &v[k]);
+        }
+        if (bad) { ndrop++; continue; }
+        if (nvalid < capacity) { user[nvalid] = (int32_t)u; act[nvalid] = ai; ts[nvalid] = t; x[nvalid] = v[0]; y[nvalid] = v[1]; z[nvalid] = v[2]; }
+        nvalid++;
+    }
+    if (dropped) *dropped = ndrop;
+    return nvalid;
+}

@@ -251,5 +251,23 @@ def synth_stream(n, first_sample=0, per_user=100000, seed=2018):
     return user, act, ts, x, y, z
 
 
+WISDM_ACTIVITIES = ("Walking", "Jogging", "Upstairs", "Downstairs", "Sitting", "Standing")
+
+
+def parse_wisdm_raw(text, activities=WISDM_ACTIVITIES):
+    """strtod / strtoll restatement of har_parse_wisdm_raw -> ((user, act, ts, x, y, z), dropped)."""
+    data = bytes(text)
+    L = lib()
+    L.orc_parse_wisdm_raw.restype = C.c_int64
+    names = (C.c_char_p * len(activities))(*[a.encode() for a in activities])
+    drop = C.c_int64()
+    cap = data.count(b";") + 1
+    user = np.zeros(cap, np.int32); act = np.zeros(cap, np.int32); ts = np.zeros(cap, np.int64)
+    x = np.zeros(cap); y = np.zeros(cap); z = np.zeros(cap)
+    n = L.orc_parse_wisdm_raw(C.c_char_p(data), C.c_int64(len(data)), names, C.c_int32(len(activities)), C.c_int64(cap),
+                              _p(user), _p(act), _p(ts), _p(x), _p(y), _p(z), C.byref(drop))
+    return (user[:n], act[:n], ts[:n], x[:n], y[:n], z[:n]), int(drop.value)
+
+
 def num_threads():
     return lib().orc_num_threads()

@@ -144,3 +144,14 @@ def test_oracle_errors_mirror_spark_messages():
     Xc = X.copy(); Xc[:, 0] = 40
     with pytest.raises(ValueError, match="requires maxBins"):
         orc.fit_forest(Xc, y, arity=[41, 0, 0], num_classes=2, max_bins=32)
+
+
+def test_oracle_raw_wisdm_ingest_rules():
+    """The strtod/strtoll restatement of the raw-text ingest: what is kept, what is dropped."""
+    from oracle import oracle as orc
+    txt = (b"33,Jogging,49105962326000,-0.6946377,12.680544,0.50395286;\n 17,Walking,1,1e-3,2.5E2,-.5;"
+           b"11,Walking,1867172313000,4.4,4.4,;\nbad;;  \n5,Flying,1,1,1,1;7,Sitting,9,1,2,3")
+    (u, a, ts, x, y, z), dropped = orc.parse_wisdm_raw(txt)
+    assert u.tolist() == [33, 17, 7] and a.tolist() == [1, 0, 4] and ts.tolist() == [49105962326000, 1, 9]
+    assert x.tolist() == [-0.6946377, 0.001, 1.0] and y.tolist() == [12.680544, 250.0, 2.0] and z.tolist() == [0.50395286, -0.5, 3.0]
+    assert dropped == 3
