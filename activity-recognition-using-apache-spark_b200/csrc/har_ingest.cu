@@ -265,3 +265,27 @@ HAR_API int har_parse_wisdm_raw(const char* d_text, int64_t nbytes, const char* 
     }
     return HAR_OK;
 }
+
+// Upper bound on the records of a text (terminators + 1): what to size the output columns with before parsing once.
+HAR_API int har_count_wisdm_raw(const char* d_text, int64_t nbytes, int64_t* max_records, har_stream_t stream) {
+    if (!max_records) return fail(HAR_E_INVALID, "har_count_wisdm_raw: max_records is NULL");
+    *max_records = 0;
+    if (nbytes <= 0) return HAR_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t nchunks = ceil_div(nbytes, ING_CHUNK);
+    DevBuf<int32_t> d_cnt;
+    DevBuf<long long> d_sum;
+    HAR_CUDA(d_cnt.alloc(nchunks, s)); HAR_CUDA(d_sum.alloc(1, s));
+    k_ing_count<<<(unsigned)ceil_div(nchunks, 256), 256, 0, s>>>(reinterpret_cast<const unsigned char*>(d_text), nbytes, d_cnt.p);
+    HAR_LAUNCH_CHECK();
+    size_t tmp_bytes = 0;
+    HAR_CUDA(cub::DeviceReduce::Sum(nullptr, tmp_bytes, d_cnt.p, d_sum.p, (int)nchunks, s));
+    DevBuf<unsigned char> d_tmp;
+    HAR_CUDA(d_tmp.alloc(tmp_bytes + 16, s));
+    HAR_CUDA(cub::DeviceReduce::Sum(d_tmp.p, tmp_bytes, d_cnt.p, d_sum.p, (int)nchunks, s));
+    long long total = 0;
+    HAR_CUDA(cudaMemcpyAsync(&total, d_sum.p, sizeof total, cudaMemcpyDeviceToHost, s));
+    HAR_CUDA(cudaStreamSynchronize(s));
+    *max_records = (int64_t)total + 1;
+    return HAR_OK;
+}

@@ -98,6 +98,7 @@ _SIGS = {
     "har_parse_wisdm_raw": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_char_p), C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
                                       C.c_void_p]),
+    "har_count_wisdm_raw": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p]),
     "har_csr_to_dense": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int64,
                                    C.c_void_p]),
 }

@@ -376,19 +376,19 @@ def parse_wisdm_raw(text, activities=WISDM_ACTIVITIES):
         COUNTERS["h2d_bytes"] += a.nbytes
         t = torch.from_numpy(a.copy()).cuda() if a.size else torch.empty(0, dtype=torch.uint8, device="cuda")
     names = (C.c_char_p * len(activities))(*[s.encode() for s in activities])
-    nrec, ndrop = C.c_int64(), C.c_int64()
-    # sizing call, then the columns
-    rc = N.lib().har_parse_wisdm_raw(ptr(t), t.numel(), names, len(activities), 0, None, None, None, None, None, None,
-                                     C.byref(nrec), C.byref(ndrop), stream())
-    if rc != 0 and nrec.value == 0:
-        N.check(rc)
-    n = nrec.value
+    nrec, ndrop, cap = C.c_int64(), C.c_int64(), C.c_int64()
+    # one cheap pass counts the terminators (an upper bound on the records); the columns are sized with it, parsed
+    # once and trimmed to the valid records
+    N.check(N.lib().har_count_wisdm_raw(ptr(t), t.numel(), C.byref(cap), stream()))
+    n = cap.value
     user = torch.empty(n, dtype=torch.int32, device="cuda"); act = torch.empty_like(user)
     ts = torch.empty(n, dtype=torch.int64, device="cuda")
     x = torch.empty(n, dtype=torch.float64, device="cuda"); y = torch.empty_like(x); z = torch.empty_like(x)
     if n:
         N.check(N.lib().har_parse_wisdm_raw(ptr(t), t.numel(), names, len(activities), n, ptr(user), ptr(act), ptr(ts), ptr(x),
                                             ptr(y), ptr(z), C.byref(nrec), C.byref(ndrop), stream()))
+    k = nrec.value
+    user, act, ts, x, y, z = (c[:k] for c in (user, act, ts, x, y, z))
     return (user, act, ts, x, y, z), int(ndrop.value)
 
 

@@ -243,6 +243,8 @@ int har_parse_wisdm_raw(const char* d_text, int64_t nbytes, const char* const* a
                         int32_t num_names, int64_t capacity, int32_t* d_user, int32_t* d_activity,
                         int64_t* d_ts, double* d_x, double* d_y, double* d_z, int64_t* num_records,
                         int64_t* num_dropped, har_stream_t stream);
+/* Upper bound on the records of such a text (terminators + 1), to size the columns before parsing once.  Synchronises. */
+int har_count_wisdm_raw(const char* d_text, int64_t nbytes, int64_t* max_records, har_stream_t stream);
 
 /* CSR -> dense row-major f64 (the reference's `features` column is a 3100-d SparseVector,
  * result.txt:110).  d_out [n][ld] is fully overwritten.  Asynchronous. */
