@@ -19,32 +19,70 @@
 namespace har {
 namespace {
 
-constexpr int ING_CHUNK = 128;          // bytes per thread in the terminator passes
+constexpr int ING_CHUNK = 4096;         // bytes per warp in the terminator passes
 constexpr int ING_MAX_NAMES = 16, ING_NAME_LEN = 24;
 
 struct ActivityNames { int n; int len[ING_MAX_NAMES]; char s[ING_MAX_NAMES][ING_NAME_LEN]; };
 
 __device__ __forceinline__ bool is_blank(unsigned char c) { return c == ' ' || c == '\t' || c == '\r' || c == '\n'; }
 
-__global__ void k_ing_count(const unsigned char* __restrict__ text, int64_t nbytes, int32_t* __restrict__ cnt) {
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t b0 = t * ING_CHUNK;
-    if (b0 >= nbytes) return;
-    const int64_t b1 = min(nbytes, b0 + ING_CHUNK);
-    int c = 0;
-    for (int64_t i = b0; i < b1; i++) c += text[i] == ';';
-    cnt[t] = c;
+// Terminator passes: a warp owns ING_CHUNK consecutive bytes and walks them in 512-byte rows, one 16-byte load per
+// lane (fully coalesced); ';' bytes are found with a SIMD-in-register compare.
+__device__ __forceinline__ uint32_t semis16(const unsigned char* __restrict__ text, int64_t nbytes, int64_t off, bool aligned) {
+    // bit k of the result: byte off + k is ';'
+    uint32_t m = 0;
+    if (aligned && off + 16 <= nbytes) {
+        const uint4 q = *reinterpret_cast<const uint4*>(text + off);
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint32_t eq = __vcmpeq4(w[j], 0x3b3b3b3bu);          // 0xff in every byte that is ';'
+            m |= ((eq & 1u) | ((eq >> 7) & 2u) | ((eq >> 14) & 4u) | ((eq >> 21) & 8u)) << (4 * j);
+        }
+    } else {
+        for (int k = 0; k < 16 && off + k < nbytes; k++) m |= (text[off + k] == ';' ? 1u : 0u) << k;
+    }
+    return m;
 }
 
-__global__ void k_ing_ends(const unsigned char* __restrict__ text, int64_t nbytes, const int32_t* __restrict__ off,
-                           int64_t* __restrict__ rec_end) {
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t b0 = t * ING_CHUNK;
+__global__ void k_ing_count(const unsigned char* __restrict__ text, int64_t nbytes, int32_t* __restrict__ cnt) {
+    const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const int64_t b0 = w * ING_CHUNK;
     if (b0 >= nbytes) return;
-    const int64_t b1 = min(nbytes, b0 + ING_CHUNK);
-    int64_t k = off[t];
-    for (int64_t i = b0; i < b1; i++) if (text[i] == ';') rec_end[k++] = i;
+    const bool aligned = (reinterpret_cast<uintptr_t>(text) & 15) == 0;
+    int c = 0;
+    for (int it = 0; it < ING_CHUNK / 512; it++) {
+        const int64_t off = b0 + it * 512 + lane * 16;
+        if (off < nbytes) c += __popc(semis16(text, nbytes, off, aligned));
+    }
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0) cnt[w] = c;
 }
+
+__global__ void k_ing_ends(const unsigned char* __restrict__ text, int64_t nbytes, const int32_t* __restrict__ off_in,
+                           int64_t* __restrict__ rec_end) {
+    const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const int64_t b0 = w * ING_CHUNK;
+    if (b0 >= nbytes) return;
+    const bool aligned = (reinterpret_cast<uintptr_t>(text) & 15) == 0;
+    int64_t k = off_in[w];
+    for (int it = 0; it < ING_CHUNK / 512; it++) {
+        const int64_t off = b0 + it * 512 + lane * 16;
+        uint32_t m = off < nbytes ? semis16(text, nbytes, off, aligned) : 0u;
+        const int c = __popc(m);
+        int incl = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { int o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += o; }
+        int64_t o = k + incl - c;
+        while (m) { const int bit = __ffs(m) - 1; rec_end[o++] = off + bit; m &= m - 1; }
+        k += __shfl_sync(0xffffffffu, incl, 31);
+    }
+}
+
+__constant__ double kPow10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16,
+                                  1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
 
 // decimal literal [p, q) -> double; 0 = ok, 1 = malformed, 2 = needs more than the exact fast path
 __device__ int parse_decimal(const unsigned char* p, const unsigned char* q, double* out) {
@@ -83,9 +121,7 @@ __device__ int parse_decimal(const unsigned char* p, const unsigned char* q, dou
         // strip trailing decimal zeros so that short literals written with padding stay on the fast path
         while (m % 10 == 0 && e10 < 0) { m /= 10; e10++; }
         if (dropped_nonzero || m >= (1ULL << 53) || e10 < -22 || e10 > 22) return 2;
-        const double P10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16,
-                                1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
-        v = e10 < 0 ? __ddiv_rn((double)m, P10[-e10]) : __dmul_rn((double)m, P10[e10]);
+        v = e10 < 0 ? __ddiv_rn((double)m, kPow10[-e10]) : __dmul_rn((double)m, kPow10[e10]);
     }
     *out = neg ? -v : v;
     return 0;
@@ -109,43 +145,39 @@ __device__ int parse_record(const unsigned char* text, int64_t a, int64_t b, con
     while (a < b && is_blank(text[a])) a++;
     while (b > a && is_blank(text[b - 1])) b--;
     if (a >= b) return 0;
-    const unsigned char* f0[6]; const unsigned char* f1[6];
-    int nf = 0;
-    const unsigned char* p = text + a; const unsigned char* e = text + b;
-    const unsigned char* s = p;
-    for (;; p++) {
-        if (p == e || *p == ',') {
-            if (nf == 6) return 2;
-            f0[nf] = s; f1[nf] = p; nf++;
-            if (p == e) break;
-            s = p + 1;
+    // fields are consumed as they are found (no table of field pointers: it would live in local memory)
+    const unsigned char* p = text + a; const unsigned char* const e = text + b;
+    long long u = 0, ts = 0;
+    int act = -1, worst = 0;
+    double v[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        const unsigned char* f0 = p;
+        while (p < e && *p != ',') p++;
+        const unsigned char* f1 = p;
+        if (k < 5) { if (p == e) return 2; p++; }       // a comma must follow the first five fields
+        else if (p != e) return 2;                      // and none the sixth
+        while (f0 < f1 && is_blank(*f0)) f0++;          // blanks around a field are tolerated, empty fields are not
+        while (f1 > f0 && is_blank(*(f1 - 1))) f1--;
+        if (f0 >= f1) return 2;
+        if (k == 0) {
+            if (parse_int64(f0, f1, &u) || u < -2147483647LL || u > 2147483647LL) return 2;
+        } else if (k == 1) {
+            const int alen = (int)(f1 - f0);
+            for (int q = 0; q < names.n && act < 0; q++) {
+                if (names.len[q] != alen) continue;
+                bool same = true;
+                for (int i = 0; i < alen && same; i++) same = names.s[q][i] == (char)f0[i];
+                if (same) act = q;
+            }
+            if (act < 0) return 2;
+        } else if (k == 2) {
+            if (parse_int64(f0, f1, &ts)) return 2;
+        } else {
+            const int rc = parse_decimal(f0, f1, &v[k - 3]);
+            if (rc == 1) return 2;
+            worst = max(worst, rc);
         }
-    }
-    if (nf != 6) return 2;
-    for (int k = 0; k < 6; k++) {                       // blanks around a field are tolerated, empty fields are not
-        while (f0[k] < f1[k] && is_blank(*f0[k])) f0[k]++;
-        while (f1[k] > f0[k] && is_blank(*(f1[k] - 1))) f1[k]--;
-        if (f0[k] >= f1[k]) return 2;
-    }
-    long long u;
-    if (parse_int64(f0[0], f1[0], &u) || u < -2147483647LL || u > 2147483647LL) return 2;
-    int act = -1;
-    const int alen = (int)(f1[1] - f0[1]);
-    for (int k = 0; k < names.n && act < 0; k++) {
-        if (names.len[k] != alen) continue;
-        bool same = true;
-        for (int i = 0; i < alen && same; i++) same = names.s[k][i] == (char)f0[1][i];
-        if (same) act = k;
-    }
-    if (act < 0) return 2;
-    long long ts;
-    if (parse_int64(f0[2], f1[2], &ts)) return 2;
-    double v[3];
-    int worst = 0;
-    for (int k = 0; k < 3; k++) {
-        const int rc = parse_decimal(f0[3 + k], f1[3 + k], &v[k]);
-        if (rc == 1) return 2;
-        worst = max(worst, rc);
     }
     if (worst == 2) return 3;
     r->user = (int)u; r->act = act; r->ts = ts; r->x = v[0]; r->y = v[1]; r->z = v[2];
@@ -157,25 +189,53 @@ __device__ __forceinline__ void record_span(const int64_t* rec_end, int64_t nrec
     *b = i < nrec ? rec_end[i] : nbytes;               // i == nrec: the unterminated tail
 }
 
-__global__ void k_ing_classify(const unsigned char* __restrict__ text, int64_t nbytes, const int64_t* __restrict__ rec_end,
+// The 128 records of a CTA are contiguous text (about 7 KB): it is copied to shared memory with coalesced loads and
+// parsed there.  Parsing straight from global memory made every byte load of a warp touch ~16 different sectors
+// (32 records, 58 bytes apart) and the two parse kernels LSU-bound (112 GB/s of text).  Spans longer than the
+// staging buffer (garbage without terminators) are parsed from global memory.
+constexpr int ING_REC_THREADS = 128, ING_STAGE = 20 * 1024;
+
+__device__ __forceinline__ const unsigned char* stage_records(const unsigned char* __restrict__ text, int64_t nbytes,
+                                                              const int64_t* __restrict__ rec_end, int64_t nrec,
+                                                              unsigned char* sm, int64_t* base_out) {
+    const int64_t i0 = (int64_t)blockIdx.x * ING_REC_THREADS;
+    const int64_t i1 = min(i0 + ING_REC_THREADS - 1, nrec);           // last record of the CTA (slot nrec = the tail)
+    int64_t a0, b0, a1, b1;
+    record_span(rec_end, nrec, nbytes, i0, &a0, &b0);
+    record_span(rec_end, nrec, nbytes, i1, &a1, &b1);
+    const int64_t len = b1 - a0;
+    if (len > ING_STAGE) { *base_out = 0; return text; }              // uniform for the CTA
+    for (int64_t k = threadIdx.x; k < len; k += ING_REC_THREADS) sm[k] = text[a0 + k];
+    __syncthreads();
+    *base_out = a0;
+    return sm;
+}
+
+__global__ void __launch_bounds__(ING_REC_THREADS) k_ing_classify(const unsigned char* __restrict__ text, int64_t nbytes, const int64_t* __restrict__ rec_end,
                                int64_t nrec, ActivityNames names, int32_t* __restrict__ valid,
                                unsigned long long* __restrict__ counters /* [dropped, unsupported] */) {
+    __shared__ __align__(16) unsigned char sm[ING_STAGE];
+    int64_t base;
+    const unsigned char* src = stage_records(text, nbytes, rec_end, nrec, sm, &base);
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i > nrec) return;
     int64_t a, b;
     record_span(rec_end, nrec, nbytes, i, &a, &b);
     Rec r;
-    const int rc = parse_record(text, a, b, names, &r);
+    const int rc = parse_record(src, a - base, b - base, names, &r);
     valid[i] = rc == 1 ? 1 : 0;
     if (rc == 2) atomicAdd(&counters[0], 1ULL);
     if (rc == 3) atomicAdd(&counters[1], 1ULL);
 }
 
-__global__ void k_ing_emit(const unsigned char* __restrict__ text, int64_t nbytes, const int64_t* __restrict__ rec_end,
+__global__ void __launch_bounds__(ING_REC_THREADS) k_ing_emit(const unsigned char* __restrict__ text, int64_t nbytes, const int64_t* __restrict__ rec_end,
                            int64_t nrec, ActivityNames names, const int32_t* __restrict__ valid,
                            const int32_t* __restrict__ pos, int64_t capacity, int32_t* __restrict__ user,
                            int32_t* __restrict__ act, int64_t* __restrict__ ts, double* __restrict__ x,
                            double* __restrict__ y, double* __restrict__ z) {
+    __shared__ __align__(16) unsigned char sm[ING_STAGE];
+    int64_t base;
+    const unsigned char* src = stage_records(text, nbytes, rec_end, nrec, sm, &base);
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i > nrec || !valid[i]) return;
     const int64_t o = pos[i];
@@ -183,7 +243,7 @@ __global__ void k_ing_emit(const unsigned char* __restrict__ text, int64_t nbyte
     int64_t a, b;
     record_span(rec_end, nrec, nbytes, i, &a, &b);
     Rec r;
-    parse_record(text, a, b, names, &r);
+    parse_record(src, a - base, b - base, names, &r);
     user[o] = r.user; act[o] = r.act; ts[o] = r.ts; x[o] = r.x; y[o] = r.y; z[o] = r.z;
 }
 
@@ -217,7 +277,7 @@ HAR_API int har_parse_wisdm_raw(const char* d_text, int64_t nbytes, const char* 
     DevBuf<int32_t> d_cnt, d_off;
     HAR_CUDA(d_cnt.alloc(nchunks + 1, s)); HAR_CUDA(d_off.alloc(nchunks + 1, s));
     HAR_CUDA(cudaMemsetAsync(d_cnt.p, 0, sizeof(int32_t) * (nchunks + 1), s));
-    k_ing_count<<<(unsigned)ceil_div(nchunks, 256), 256, 0, s>>>(text, nbytes, d_cnt.p);
+    k_ing_count<<<(unsigned)ceil_div(nchunks * 32, 256), 256, 0, s>>>(text, nbytes, d_cnt.p);
     HAR_LAUNCH_CHECK();
     size_t tmp_bytes = 0;
     HAR_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_cnt.p, d_off.p, (int)(nchunks + 1), s));
@@ -230,15 +290,15 @@ HAR_API int har_parse_wisdm_raw(const char* d_text, int64_t nbytes, const char* 
     const int64_t nrec = nrec32;                                     // terminated records; slot nrec is the tail
     DevBuf<int64_t> d_end;
     HAR_CUDA(d_end.alloc(nrec + 1, s));
-    k_ing_ends<<<(unsigned)ceil_div(nchunks, 256), 256, 0, s>>>(text, nbytes, d_off.p, d_end.p);
+    k_ing_ends<<<(unsigned)ceil_div(nchunks * 32, 256), 256, 0, s>>>(text, nbytes, d_off.p, d_end.p);
     HAR_LAUNCH_CHECK();
     DevBuf<int32_t> d_valid, d_pos;
     DevBuf<unsigned long long> d_counters;
     HAR_CUDA(d_valid.alloc(nrec + 2, s)); HAR_CUDA(d_pos.alloc(nrec + 2, s)); HAR_CUDA(d_counters.alloc(2, s));
     HAR_CUDA(cudaMemsetAsync(d_counters.p, 0, 2 * sizeof(unsigned long long), s));
     HAR_CUDA(cudaMemsetAsync(d_valid.p, 0, sizeof(int32_t) * (nrec + 2), s));
-    const unsigned gb = (unsigned)ceil_div(nrec + 1, 128);
-    k_ing_classify<<<gb, 128, 0, s>>>(text, nbytes, d_end.p, nrec, names, d_valid.p, d_counters.p);
+    const unsigned gb = (unsigned)ceil_div(nrec + 1, ING_REC_THREADS);
+    k_ing_classify<<<gb, ING_REC_THREADS, 0, s>>>(text, nbytes, d_end.p, nrec, names, d_valid.p, d_counters.p);
     HAR_LAUNCH_CHECK();
     size_t tmp2 = 0;
     HAR_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp2, d_valid.p, d_pos.p, (int)(nrec + 2), s));
@@ -259,7 +319,7 @@ HAR_API int har_parse_wisdm_raw(const char* d_text, int64_t nbytes, const char* 
     if (nvalid > capacity)
         return fail(HAR_E_INVALID, "har_parse_wisdm_raw: %d records do not fit the output capacity %lld", nvalid, (long long)capacity);
     if (nvalid > 0) {
-        k_ing_emit<<<gb, 128, 0, s>>>(text, nbytes, d_end.p, nrec, names, d_valid.p, d_pos.p, capacity, d_user, d_activity, d_ts,
+        k_ing_emit<<<gb, ING_REC_THREADS, 0, s>>>(text, nbytes, d_end.p, nrec, names, d_valid.p, d_pos.p, capacity, d_user, d_activity, d_ts,
                                       d_x, d_y, d_z);
         HAR_LAUNCH_CHECK();
     }
@@ -276,7 +336,7 @@ HAR_API int har_count_wisdm_raw(const char* d_text, int64_t nbytes, int64_t* max
     DevBuf<int32_t> d_cnt;
     DevBuf<long long> d_sum;
     HAR_CUDA(d_cnt.alloc(nchunks, s)); HAR_CUDA(d_sum.alloc(1, s));
-    k_ing_count<<<(unsigned)ceil_div(nchunks, 256), 256, 0, s>>>(reinterpret_cast<const unsigned char*>(d_text), nbytes, d_cnt.p);
+    k_ing_count<<<(unsigned)ceil_div(nchunks * 32, 256), 256, 0, s>>>(reinterpret_cast<const unsigned char*>(d_text), nbytes, d_cnt.p);
     HAR_LAUNCH_CHECK();
     size_t tmp_bytes = 0;
     HAR_CUDA(cub::DeviceReduce::Sum(nullptr, tmp_bytes, d_cnt.p, d_sum.p, (int)nchunks, s));
