@@ -222,6 +222,31 @@ def test_device_grown_forest_equals_host_driven_fit(monkeypatch):
         assert np.array_equal(_bits(a), _bits(b))
 
 
+@pytest.mark.parametrize("kw", [
+    dict(num_trees=5, max_depth=1),
+    dict(num_trees=5, max_depth=2),
+    dict(num_trees=4, max_depth=7, min_instances_per_node=40, min_info_gain=0.005),
+    dict(num_trees=3, max_depth=6, impurity="entropy"),
+    dict(num_trees=2, max_depth=14, subsampling_rate=0.3),
+    dict(num_trees=150, max_depth=4),
+    dict(num_trees=1, max_depth=9, subsampling_rate=0.8),
+])
+def test_device_grown_forest_parameter_corners(kw):
+    """The device-driven path (all features) under the parameters that change its control flow: depths below the
+    sibling-subtraction threshold, leaf rules (minInstancesPerNode / minInfoGain), entropy, deep sparse trees, many
+    trees, a single bagged tree."""
+    X, y, arity = synth_tree_data(9000, F=9, C=3, seed=31, n_cat_unordered=1, n_cat_ordered=1)
+    po = [0, 1000, 1000, 4500, 9000]                                   # an empty partition too
+    g, o = _fit_both(X, y, arity, num_classes=3, feature_subset="all", seed=13, part_off=po, **kw)
+    assert_forest_equal(o, g, exact_fp=kw.get("impurity") != "entropy")
+    assert g.num_groups == o.num_groups
+    raw, prob, pred = [t.cpu().numpy() for t in g.predict(X[:2000], is_forest=kw["num_trees"] > 1)]
+    ro, po_, pr = orc.predict(o, X[:2000], is_forest=kw["num_trees"] > 1)
+    assert np.array_equal(pred, pr)
+    if kw.get("impurity") != "entropy":
+        assert np.array_equal(_bits(raw), _bits(ro))
+
+
 def test_count_division_is_the_ieee_division():
     """k_best_split divides class counts with the fast path of __ddiv_rn spelled out (no range checks, no slow
     path for zero numerators); over 2^28 random and edge operand pairs of its domain it must equal __ddiv_rn
