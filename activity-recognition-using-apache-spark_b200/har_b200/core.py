@@ -93,6 +93,11 @@ def div_check(n, seed=1):
     return int(m.value)
 
 
+def release_scratch():
+    """Frees the device scratch arena the calling thread's fits keep between calls (har_scratch_release)."""
+    N.lib().har_scratch_release()
+
+
 def launch_count(reset=False):
     return int(N.lib().har_debug_launch_count(1 if reset else 0))
 
