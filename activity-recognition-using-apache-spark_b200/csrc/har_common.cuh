@@ -26,6 +26,11 @@ long long launches_since_reset();
 void reset_launches();
 // int32 sum all-reduce of a device buffer over the ranks of `d` (no-op for one rank); har_comm.cu
 int dist_allreduce(const har_dist* d, void* buf, int64_t count, cudaStream_t s);
+// true when the group's exchanges run on the library's own NCCL communicator (collective on first use)
+bool dist_has_nccl(const har_dist* d, cudaStream_t s);
+// node-sharded exchange (NCCL only): sum of int32 segment r lands on rank r / byte segment r goes from rank r to all
+int dist_reduce_segments(const har_dist* d, int32_t* buf, const int64_t* off, cudaStream_t s);
+int dist_gather_segments(const har_dist* d, void* buf, const int64_t* off, cudaStream_t s);
 
 // optional CUDA-event timing of selected kernels (har_debug_profile_*; off by default)
 enum ProfId { PROF_NODE_HIST = 0, PROF_BEST_SPLIT, PROF_PART_COUNT, PROF_PART_SCATTER, PROF_WINDOW_FEATURES,

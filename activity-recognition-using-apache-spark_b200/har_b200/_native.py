@@ -34,7 +34,7 @@ ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_
 class Dist(C.Structure):
     _fields_ = [("rank", C.c_int32), ("world_size", C.c_int32), ("global_rows", C.c_int64),
                 ("partition_offset", C.c_int32), ("total_partitions", C.c_int32),
-                ("allreduce_i32", ALLREDUCE_FN), ("ctx", C.c_void_p)]
+                ("allreduce_i32", ALLREDUCE_FN), ("ctx", C.c_void_p), ("group_id", C.c_uint64)]
 
 
 def build(force=False, verbose=False):
@@ -59,6 +59,8 @@ _SIGS = {
     "har_set_device": (C.c_int, [C.c_int32]),
     "har_stream_synchronize": (C.c_int, [C.c_void_p]),
     "har_scratch_release": (None, []),
+    "har_dist_transport": (C.c_int, [C.POINTER(Dist), C.c_char_p, C.c_int32]),
+    "har_dist_release": (None, []),
     "har_debug_launch_count": (C.c_longlong, [C.c_int]),
     "har_debug_comm_stats": (None, [C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), C.POINTER(C.c_int), C.c_int]),
     "har_debug_div_check": (C.c_int, [C.c_longlong, C.c_ulonglong, C.POINTER(C.c_ulonglong), C.c_void_p]),

@@ -37,14 +37,32 @@ def wrap_i32(ptr, count, device=None):
     return torch.frombuffer(buf, dtype=torch.int32)
 
 
+_GROUP_IDS = {}
+
+
+def _group_id(td, group):
+    """Stable id of a torch process group inside this process (the library keys its transport decision on it)."""
+    key = id(group) if group is not None else 0
+    if key not in _GROUP_IDS:
+        _GROUP_IDS[key] = len(_GROUP_IDS) + 1
+    return _GROUP_IDS[key]
+
+
 class Dist:
-    """Builds the har_dist struct; keeps the ctypes callback alive."""
+    """Builds the har_dist struct; keeps the ctypes callback alive.
+
+    The callback hands the library's buffer to torch.distributed.all_reduce.  With an NCCL group the device buffer is
+    reduced in place on the stream the library names.  With a group that cannot reduce device memory (gloo) the
+    buffer is staged through the host: copy down on that stream, reduce on the CPU, copy back — slow, but it lets
+    several ranks share one GPU (tests) and keeps the collective path usable without NCCL.  host_buffers=True: the
+    pointers the callback receives are host pointers (CPU-only unit tests of the callback)."""
 
     def __init__(self, global_rows, partition_offset, total_partitions, group=None, host_buffers=False):
         import torch.distributed as td
         self._td, self._group = td, group
         self.rank, self.world = td.get_rank(group), td.get_world_size(group)
         self._device = None if host_buffers else torch.device("cuda", torch.cuda.current_device())
+        self._staged = (not host_buffers) and td.get_backend(group) != "nccl"
         self.calls = 0
         self.bytes = 0
 
@@ -53,13 +71,20 @@ class Dist:
         def _cb(ctx, ptr, count, stream):
             try:
                 t = wrap_i32(ptr, count, self._device)
-                if self._device is not None and stream:
+                if self._device is not None:
                     # the library may call from a stream of its own (one per tree set): order the collective there
                     st = streams.get(stream)
                     if st is None:
-                        st = streams[stream] = torch.cuda.ExternalStream(stream, device=self._device)
+                        st = streams[stream] = (torch.cuda.ExternalStream(stream, device=self._device) if stream
+                                                else torch.cuda.default_stream(self._device))
                     with torch.cuda.stream(st):
-                        td.all_reduce(t, op=td.ReduceOp.SUM, group=self._group)
+                        if self._staged:
+                            h = t.cpu()                       # synchronises `st`
+                            td.all_reduce(h, op=td.ReduceOp.SUM, group=self._group)
+                            t.copy_(h)
+                            st.synchronize()
+                        else:
+                            td.all_reduce(t, op=td.ReduceOp.SUM, group=self._group)
                 else:
                     td.all_reduce(t, op=td.ReduceOp.SUM, group=self._group)
                 self.calls += 1
@@ -71,7 +96,18 @@ class Dist:
 
         self._cb = N.ALLREDUCE_FN(_cb)
         self.struct = N.Dist(self.rank, self.world, int(global_rows), int(partition_offset), int(total_partitions),
-                             self._cb, None)
+                             self._cb, None, _group_id(td, group))
+
+    def transport(self):
+        """(1 library NCCL communicator | 0 callback | -1 undecided, reason) — har_dist_transport."""
+        buf = C.create_string_buffer(512)
+        rc = N.lib().har_dist_transport(C.byref(self.struct), buf, 512)
+        return rc, buf.value.decode("utf-8", "replace")
+
+
+def release():
+    """Destroys the library's cached NCCL communicators (har_dist_release); call before destroy_process_group."""
+    N.lib().har_dist_release()
 
 
 def exchange_shard_layout(local_rows, local_partitions, group=None):

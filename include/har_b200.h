@@ -139,10 +139,11 @@ typedef struct har_fit_params {
  * RandomForest.findBestSplits.  Return 0 on success. */
 typedef int (*har_allreduce_i32_fn)(void* ctx, void* d_buf, int64_t count, har_stream_t stream);
 /* With world_size > 1 the callback always carries the small exchanges (row counts, the findSplits sample).  For the
- * per-batch counters the library prefers a communicator of its own: if libnccl.so.2 is already loaded in the
- * process it creates one over the same ranks (the unique id is exchanged once through this callback) and calls
- * ncclAllReduce on its own streams; HAR_NCCL=0 in the environment, or no NCCL in the process, keeps everything
- * on the callback.  The callback must honour `stream` (the library may use streams of its own). */
+ * per-batch counters the library prefers a communicator of its own: if libnccl.so.2 is already loaded in every
+ * rank's process it creates one over the same ranks (the unique id is exchanged once through this callback, and the
+ * ranks agree through it that all of them got a communicator) and issues the NCCL calls on its own streams;
+ * HAR_NCCL=0 in the environment, or no NCCL in some rank's process, keeps everything on the callback for every rank.
+ * The callback must honour `stream` (the library may use streams of its own). */
 
 typedef struct har_dist {
     int32_t rank, world_size;
@@ -151,7 +152,18 @@ typedef struct har_dist {
     int32_t total_partitions;
     har_allreduce_i32_fn allreduce_i32;
     void* ctx;
+    uint64_t group_id;               /* names the group of ranks behind the callback: fits that pass the same
+                                        (group_id, world_size, rank) on one device share one transport decision and one
+                                        library communicator; use a different value for a different set of processes */
 } har_dist;
+
+/* Which transport carries the per-batch exchanges of this group: 1 = the library's own NCCL communicator, 0 = the
+ * caller's callback (the reason is copied to `why`, NUL-terminated, at most cap bytes), -1 = not decided yet (the
+ * decision is made collectively inside the group's first exchange and is the same on every rank).
+ * har_dist_release destroys the cached communicators (call it before the process group goes away).
+ * No reference counterpart: Spark's executors own their shuffle connections. */
+int har_dist_transport(const har_dist* dist, char* why, int32_t cap);
+void har_dist_release(void);
 
 /* a4 — RandomForest.findSplits / findSplitsForContinuousFeature: quantile thresholds of every
  * continuous feature (arity[f] <= 1) from the Bernoulli row sample MLlib draws.

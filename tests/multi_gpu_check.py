@@ -14,7 +14,7 @@ import numpy as np
 import torch
 import torch.distributed as td
 from har_b200 import core, synth
-from har_b200.dist import Dist
+from har_b200.dist import Dist, release
 
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
@@ -61,4 +61,5 @@ for kw in (dict(num_trees=20, max_depth=8, feature_subset="all"), dict(num_trees
               "ranks and to the 1-GPU forest" % (kw, fo.total_nodes, calls, dist.calls, nbytes / 1e6,
                                                  "library NCCL communicator" if via else "callback only", world))
     td.barrier()
+release()
 td.destroy_process_group()

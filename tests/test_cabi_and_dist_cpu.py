@@ -54,7 +54,7 @@ def test_product_package_never_imports_the_oracle():
 def test_struct_layouts_match_the_header():
     from har_b200 import _native
     assert C.sizeof(_native.FitParams) == 8 * 4 + 2 * 8 + 2 * 8
-    assert C.sizeof(_native.Dist) == 4 + 4 + 8 + 4 + 4 + 8 + 8
+    assert C.sizeof(_native.Dist) == 4 + 4 + 8 + 4 + 4 + 8 + 8 + 8
 
 
 def test_estimator_params_follow_spark_2_4():
