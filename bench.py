@@ -48,54 +48,107 @@ def parse():
     ap.add_argument("--trees", type=int, default=100)
     ap.add_argument("--depth", type=int, default=10)
     ap.add_argument("--partitions", type=int, default=1024, help="Spark partitions per GPU shard (bagging streams)")
-    ap.add_argument("--cpu-sample", type=int, default=30_000_000, help="stream samples of the bounded CPU baseline")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="stream samples per step of the CPU arm / cpu_baseline "
+                    "(0 = one GPU's whole shard, --samples; it is shrunk only if the run would not end within minutes)")
+    ap.add_argument("--strong", action="store_true", help="strong scaling: --samples is the job total, split over the GPUs (config 4)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-wisdm", action="store_true", help="skip the WISDM (configs 1-2) fit/transform timings")
+    ap.add_argument("--no-config5", action="store_true", help="skip the 500-tree depth-12 predict sweep (config 5)")
+    ap.add_argument("--config5-rows", type=int, default=100_000_000)
     return ap.parse_args()
 
 
 # ---------------------------------------------------------------------------------------------------
-def cpu_pass(n_samples, trees, depth, per_user, seed=2018):
-    """One pass of the path on the host cores with the oracle; returns (seconds, windows)."""
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def load_oracle():
+    """The CPU arm uses every core this process may run on.  torchrun exports OMP_NUM_THREADS=1 to its children, so
+    the count is set explicitly: in the environment before libgomp is loaded, and through omp_set_num_threads."""
+    cores = host_cores()
+    os.environ["OMP_NUM_THREADS"] = str(cores)
     from oracle import oracle as orc
+    orc.build()
+    orc.set_num_threads(cores)
+    return orc, orc.num_threads()
+
+
+def cpu_partitions(args, n_samples):
+    """Same rows per Spark partition as the GPU arm (bagging streams are per partition)."""
+    return max(1, int(round(args.partitions * n_samples / float(samples_per_gpu(args)))))
+
+
+def cpu_pass(orc, stream, trees, depth, partitions, seed=2018):
+    """One pass of the path on the host cores with the oracle over a resident stream; returns (seconds, windows)."""
     import numpy as np
-    u, a, ts, x, y, z = orc.synth_stream(n_samples, 0, per_user, seed)
+    u, a, ts, x, y, z = stream
     t0 = time.perf_counter()
     ws = orc.window_segments(u, a, ts, L=WINDOW)
     feats = orc.window_features(x, y, z, ts, ws, L=WINDOW)
     labels = a[ws].astype(np.float64)
-    parts = max(1, len(ws) // 500)
-    po = [(len(ws) * k) // parts for k in range(parts + 1)]
+    po = [(len(ws) * k) // partitions for k in range(partitions + 1)]
     fo = orc.fit_forest(feats, labels, num_classes=6, num_trees=trees, max_depth=depth, max_bins=32,
                         feature_subset="all", seed=seed, part_off=po)
     orc.predict(fo, feats, is_forest=True)
     return time.perf_counter() - t0, len(ws)
 
 
+def samples_per_gpu(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    return args.samples // world if args.strong else args.samples
+
+
 def run_reference(args):
+    """The reference's CPU implementation of the path: Spark cannot run here (no JVM), so this is the C/OpenMP
+    restatement of MLlib's algorithm (oracle/), on every host core, over the stream of ONE GPU's shard of our arm's
+    workload: same generator, same bout layout (per_user), same rows per partition, same forest settings."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    from oracle import oracle as orc
-    cores = orc.num_threads()
-    n = args.cpu_sample
-    per_user = max(n // max(args.users // 10, 1), 20000)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    orc, cores = load_oracle()
+    shard = samples_per_gpu(args)
+    n = args.cpu_sample if args.cpu_sample > 0 else shard
+    per_user = max(shard // args.users, 1)
+    stream = orc.synth_stream(n, 0, per_user, 2018)
+    budget_s = 240.0
+    passes = args.steps + args.warmup
+    shrunk = None
+    dt0, _ = cpu_pass(orc, tuple(c[:min(n, 2_000_000)] for c in stream), args.trees, args.depth, cpu_partitions(args, min(n, 2_000_000)))
+    est = dt0 * n / float(min(n, 2_000_000))
+    if est * passes > budget_s and n > 2_000_000:
+        n2 = max(2_000_000, int(n * budget_s / (est * passes)))
+        shrunk = "shrunk from %d to %d samples per step so that %d passes end within %d s" % (n, n2, passes, int(budget_s))
+        n = n2
+        stream = tuple(c[:n] for c in stream)
+    P = cpu_partitions(args, n)
     for _ in range(args.warmup):
-        cpu_pass(min(n, 1_000_000), args.trees, args.depth, per_user)
-    times = []
+        cpu_pass(orc, stream, args.trees, args.depth, P)
+    times, nw = [], 0
     for _ in range(args.steps):
-        dt, nw = cpu_pass(n, args.trees, args.depth, per_user)
+        dt, nw = cpu_pass(orc, stream, args.trees, args.depth, P)
         times.append(dt)
     total = sum(times)
     value = n * args.steps / total
-    sample = ("%d samples (%d windows) per step of the config-3 stream shape: window transform + RF(%d trees, depth %d, "
-              "all features) fit + predict; C/OpenMP oracle port of MLlib 2.4 (Spark/JVM unavailable on this box)"
-              % (n, nw, args.trees, args.depth))
+    sample = ("%d samples (%d windows, %d partitions, %d samples per user) per step = %s of the workload's stream, same generator "
+              "and bout layout: window transform + RF(%d trees, depth %d, all features) fit + predict; C/OpenMP restatement of "
+              "MLlib 2.4 (Spark/JVM unavailable on this box), %d threads, built %s%s"
+              % (n, nw, P, per_user, "one GPU's whole shard" if n == shard else "the first %.0f %% of one GPU's shard" % (100.0 * n / shard),
+                 args.trees, args.depth, cores, orc.CFLAGS, ("; " + shrunk) if shrunk else ""))
+    cfg = workload_config(args, world)
+    cfg["samples_per_step_run"] = n
+    cfg["partitions_run"] = P
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
+            "scaling": "strong" if args.strong else "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args, args.gpus),
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "config": cfg,
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "flags": orc.CFLAGS},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "spark": "unavailable on this box (no JVM / pyspark 2.4)"}
     print(json.dumps(line))
@@ -103,13 +156,14 @@ def run_reference(args):
 
 
 def workload_config(args, world):
-    return {"workload": "config 3: synthetic tri-axial stream (20 Hz, %d users/GPU, 6 classes) -> 10 s window features -> "
+    spg = args.samples // world if args.strong else args.samples
+    return {"workload": "config %s: synthetic tri-axial stream (20 Hz, %d users/GPU, 6 classes) -> 10 s window features -> "
                         "RandomForest(%d trees, maxDepth %d, maxBins 32, subsamplingRate 1, featureSubsetStrategy all) fit + "
-                        "predict" % (args.users, args.trees, args.depth),
-            "samples_per_gpu": args.samples, "global_samples": args.samples * world, "window": WINDOW, "features": F,
+                        "predict" % ("4 (strong scaling)" if args.strong else "3", args.users, args.trees, args.depth),
+            "samples_per_gpu": spg, "global_samples": spg * world, "window": WINDOW, "features": F,
             "trees": args.trees, "max_depth": args.depth, "partitions_per_gpu": args.partitions,
-            "parallelism": "row-sharded x%d, int32 histogram all-reduce" % world,
-            "l2": "inputs (%.1f GB/GPU) exceed L2; no flush needed" % (args.samples * 40 / 1e9)}
+            "parallelism": "row-sharded x%d, int32 histogram exchange over NCCL" % world,
+            "l2": "inputs (%.1f GB/GPU) exceed L2; no flush needed" % (spg * 40 / 1e9)}
 
 
 class ClockSampler:
@@ -227,7 +281,7 @@ def run_ours(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         td.init_process_group("nccl", device_id=torch.device("cuda", local))
-    n = args.samples
+    n = samples_per_gpu(args)
     per_user = max(n // args.users, 1)
     user, act, ts, x, y, z = synth.synth_stream(n, first_sample=rank * n, per_user=per_user, seed=2018)
     torch.cuda.synchronize()
@@ -267,10 +321,25 @@ def run_ours(args):
             td.barrier()
         torch.cuda.synchronize()
 
+    def forest_signature(fo):
+        """What every rank must agree on: node count, sum of split features, of threshold bits, of leaf/node class counts."""
+        return torch.tensor([fo.total_nodes, int(fo.feature.astype(np.int64).sum()),
+                             int(fo.threshold.view(np.int64).astype(np.uint64).sum(dtype=np.uint64) % np.uint64(1 << 40)),
+                             int(fo.stats.sum())], dtype=torch.int64, device="cuda")
+
+    def ranks_agree(fo):
+        if world == 1:
+            return None
+        sig = forest_signature(fo)
+        sigs = [torch.zeros_like(sig) for _ in range(world)]
+        td.all_gather(sigs, sig)
+        return all(bool((s_ == sigs[0]).all()) for s_ in sigs)
+
     for _ in range(args.warmup):
         forest, pred, labels = device_step()
     barrier()
     train_acc = float((pred == labels).double().mean().item())
+    agree = ranks_agree(forest)
     core.profile(enable=True, reset=True)
     core.launch_count(reset=True)
     if rank == 0:
@@ -282,7 +351,7 @@ def run_ours(args):
     e0.record()
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     # with several ranks only after the last step: a query in the middle would make the other ranks wait for rank 0
-    sample_at = ({args.steps // 2, args.steps - 1} if world == 1 else {args.steps - 1}) if rank == 0 else set()
+    sample_at = (set(range(args.steps)) if world == 1 else {args.steps - 1}) if rank == 0 else set()
     query_spans = []
     for i in range(args.steps):
         starts[i].record()
@@ -302,6 +371,8 @@ def run_ours(args):
     barrier()
     launches = core.launch_count()
     prof = core.profile(enable=False)
+    if world > 1:
+        agree = bool(agree) and bool(ranks_agree(rec[-1][3]))
     clk = clocks.stop() if rank == 0 else None
     excluded_ms = sum(a.elapsed_time(b) for a, b in query_spans)
     ms_total = e0.elapsed_time(e1) - excluded_ms
@@ -353,26 +424,57 @@ def run_ours(args):
         tt = torch.tensor([wall], dtype=torch.float64, device="cuda")
         if world > 1:
             td.all_reduce(tt, op=td.ReduceOp.MAX)
+        h2d_gbs = torch.tensor([core.COUNTERS["h2d_bytes"] / k_e2e / wall / 1e9], dtype=torch.float64, device="cuda")
+        h2d_all = [torch.zeros_like(h2d_gbs) for _ in range(world)]
+        if world > 1:
+            td.all_gather(h2d_all, h2d_gbs)
+        else:
+            h2d_all = [h2d_gbs]
         e2e = {"value": n * world / float(tt.item()), "unit": UNIT,
+               "h2d_gb_per_s_of_step_per_rank": [round(float(v.item()), 2) for v in h2d_all],
                "h2d_bytes_per_step": core.COUNTERS["h2d_bytes"] // k_e2e, "d2h_bytes_per_step": core.COUNTERS["d2h_bytes"] // k_e2e,
                "ms_per_step": 1e3 * float(tt.item()), "api": "WisdmWindowFeaturizer.transform -> RandomForestClassifier.fit -> "
                "model.transform on host (pinned) columns", "steps": k_e2e}
         del raw_df, host
 
-    # ---- CPU baseline (rank 0, N = 1 only) ------------------------------------------------------------
+    # ---- CPU baseline (rank 0, N = 1 only): the oracle on every host core, one pass over the same stream ------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        from oracle import oracle as orc
-        cs = args.cpu_sample
-        dt, cw = cpu_pass(cs, args.trees, args.depth, max(cs // max(args.users // 10, 1), 20000))
-        cpu = {"value": cs / dt, "unit": UNIT, "cores": orc.num_threads(), "kind": "port",
-               "sample": "%d samples (%d windows) of the same stream shape, same RF settings, one pass (%.1f s); C/OpenMP oracle "
-                         "port of MLlib 2.4 — Spark local[N] is unavailable on this box (no JVM)" % (cs, cw, dt)}
+        orc, cores = load_oracle()
+        cs = args.cpu_sample if args.cpu_sample > 0 else n
+        cs = min(cs, n)
+        stream = tuple(t_[:cs].cpu().numpy() for t_ in (user, act, ts, x, y, z))
+        dt, cw = cpu_pass(orc, stream, args.trees, args.depth, cpu_partitions(args, cs))
+        del stream
+        cpu = {"value": cs / dt, "unit": UNIT, "cores": cores, "kind": "port", "flags": orc.CFLAGS,
+               "sample": "%d samples (%d windows) = %s the GPU arm timed, same RF settings and rows per partition, one pass "
+                         "(%.1f s); C/OpenMP restatement of MLlib 2.4 — Spark local[N] is unavailable on this box (no JVM)"
+                         % (cs, cw, "the whole stream" if cs == n else "a prefix of the stream", dt)}
 
+    # ---- configs 1-2: the reference's own frame (WISDM transformed table, 3793 x 3100 train rows) through the pyspark surface
+    wisdm = None
+    if rank == 0 and world == 1 and not args.no_wisdm:
+        try:
+            wisdm = wisdm_timings()
+        except Exception as e:                           # the headline line must not die on an auxiliary timing
+            wisdm = {"error": repr(e)}
+
+    # ---- config 5: 500 trees x depth 12 scored over 1e8 windows (outside the timed region) ------------------------------
+    config5 = None
+    if rank == 0 and world == 1 and not args.no_config5:
+        try:
+            config5 = config5_predict(args, feat, (user, act, ts, x, y, z), clocks)
+        except Exception as e:
+            config5 = {"error": repr(e)}
+
+    if world > 1:
+        from har_b200 import dist as hd
+        barrier()
+        hd.release()
     if rank != 0:
         if world > 1:
             td.destroy_process_group()
-        return 0
+        return 0 if agree in (None, True) else 3
 
     # ---- roofline of the dominant kernel (live CUDA-event durations from inside the library) ----------
     peaks, peak_src = measured_peaks()
@@ -403,7 +505,10 @@ def run_ours(args):
         if name in alg_bytes and k["ms_per_step"] > 0:
             ach = alg_bytes[name] * k["units_per_step"] / (k["ms_per_step"] * 1e-3) / 1e9
             roofs[name] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                           "traffic": traffic.get(name), "ms_per_step": k["ms_per_step"],
+                           "traffic": traffic.get(name),
+                           "traffic_source": "ncu --set full capture of this kernel kept in profiles/traffic.json (an earlier run of "
+                                             "the same command), not measured in this run",
+                           "ms_per_step": k["ms_per_step"],
                            "launches_per_step": k["launches_per_step"],
                            "avg_launch_ms": k["ms_per_step"] / k["launches_per_step"],
                            "algorithmic_bytes_per_launch": alg_bytes[name] * k["units_per_step"] / k["launches_per_step"]}
@@ -430,19 +535,117 @@ def run_ours(args):
     window_roof["frac"] = window_roof["achieved"] / peak
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.strong else "weak",
+            "vs_baseline": None, "dtype": "f64", "ranks_agree": agree,
             "data": "synthetic", "config": workload_config(args, world),
             "stages": {"window_features_samples_per_s": n / (win_ms * 1e-3), "window_ms": win_ms, "rf_fit_s": stage["fit_ms"] * 1e-3,
                        "predict_ms": stage["predict_ms"], "windows_per_gpu": nw, "forest_nodes": rec[-1][2],
                        "node_groups": rec[-1][3].num_groups, "device_batches": rec[-1][4], "allreduce_calls": rec[-1][5][0], "allreduce_via": "library NCCL communicator" if rec[-1][5][2] else "caller's callback (torch.distributed)",
-                       "allreduce_bytes": rec[-1][5][1], "train_accuracy": train_acc},
+                       "allreduce_bytes": rec[-1][5][1], "train_accuracy": train_acc, "wisdm": wisdm},
+            "config5": config5,
             "roofline": roofline, "window_stage_roofline": window_roof, "kernels": roofs,
             "step_ms": [starts[i].elapsed_time(marks[i + 1]) for i in range(args.steps)],
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk}
     print(json.dumps(line))
     if world > 1:
         td.destroy_process_group()
+    if agree is False:
+        print("bench.py: the ranks do not hold the same forest", file=sys.stderr)
+        return 3
     return 0
+
+
+REFERENCE_TIMES = {   # the reference's own Spark run, hardware unstated (Main/wisdm_main_ver_0.0/main_result/result.txt)
+    "dt_fit_s": 12.189, "dt_transform_lazy_s": 0.074,      # result.txt:232-233 (DecisionTree maxDepth 3)
+    "rf_fit_s": 20.472, "rf_transform_lazy_s": 0.149}      # result.txt:277-278 (RandomForest 100 trees, depth 4, auto)
+
+
+def wisdm_timings(repeats=3):
+    """dt.fit / rf.fit / transform wall-clock on the reference's own frame (Main/main.py:297-305, 478-486), through the
+    pyspark-shaped estimators, host columns in and host-readable columns out; plus config 2's forest (100 trees, depth
+    10, all 3100 features).  transform() is forced (the prediction column is read), unlike Spark's lazy transform."""
+    import gzip
+    import tempfile
+    import numpy as np
+    from har_b200.pipeline import build_wisdm_frames
+    from pyspark.ml.classification import DecisionTreeClassifier, RandomForestClassifier
+    fx = os.path.join(ROOT, "tests", "golden", "wisdm_transformed.csv.gz")
+    with tempfile.TemporaryDirectory() as tmp:
+        path = os.path.join(tmp, "wisdm_data.csv")
+        with gzip.open(fx, "rb") as src, open(path, "wb") as dst:
+            dst.write(src.read())
+        data, df, train, test, _ = build_wisdm_frames(path)
+    keep = [c for c in test.columns if c in ("label", "features", "UID")]
+    test_data = test.select(keep)
+
+    def timed(est):
+        fit_s, tr_s, model, correct = [], [], None, 0
+        for i in range(repeats + 1):                       # first round is a warm-up
+            t0 = time.perf_counter()
+            model = est.fit(train)
+            t1 = time.perf_counter()
+            out = model.transform(test_data)
+            pred = np.asarray(out._cols["prediction"])
+            t2 = time.perf_counter()
+            if i:
+                fit_s.append(t1 - t0); tr_s.append(t2 - t1)
+            correct = int((pred == np.asarray(out._cols["label"])).sum())
+        return sorted(fit_s)[len(fit_s) // 2], sorted(tr_s)[len(tr_s) // 2], correct, model
+
+    out = {"rows_train": train.count(), "rows_test": test.count(), "features": 3100, "reference": REFERENCE_TIMES,
+           "note": "median of %d after one warm-up; fit and transform are eager here (Spark's transform is lazy)" % repeats}
+    f, t, c, m = timed(DecisionTreeClassifier(featuresCol="features", labelCol="label", maxDepth=3))
+    out["dt_depth3"] = {"fit_s": f, "transform_s": t, "correct_of_1625": c, "model": str(m).split(") ")[-1]}
+    f, t, c, m = timed(RandomForestClassifier(featuresCol="features", labelCol="label", numTrees=100, maxDepth=4, maxBins=32, seed=2018))
+    out["rf_100x4_auto"] = {"fit_s": f, "transform_s": t, "correct_of_1625": c}
+    f, t, c, m = timed(RandomForestClassifier(featuresCol="features", labelCol="label", numTrees=100, maxDepth=10, maxBins=32,
+                                              featureSubsetStrategy="all", subsamplingRate=1.0, seed=2018))
+    out["config2_rf_100x10_all"] = {"fit_s": f, "transform_s": t, "correct_of_1625": c, "total_nodes": m.totalNumNodes}
+    return out
+
+
+def config5_predict(args, feat, stream, clocks):
+    """BASELINE.json configs[4]: batched predict of a 500-tree depth-12 forest over 1e8 synthetic windows, swept over the
+    batch size.  The forest is trained on the windows of this run's stream; the rows scored are those windows' feature
+    vectors tiled with a per-copy offset (distinct rows, same distribution), resident in HBM."""
+    import torch
+    from har_b200 import core
+    feats, wu, wa, ws = feat.transform_device(*stream)
+    feats = torch.nan_to_num(feats, nan=0.0)
+    labels = wa.to(torch.float64)
+    nw = feats.shape[0]
+    forest = core.fit_forest(feats, labels, num_classes=6, num_trees=500, max_depth=12, max_bins=32, feature_subset="sqrt", seed=2018)
+    free, _ = torch.cuda.mem_get_info()
+    rows = int(min(args.config5_rows, (free * 0.6) // (F * 8 + 104)))
+    reps = -(-rows // nw)
+    X = torch.empty((rows, F), dtype=torch.float64, device="cuda")
+    for r in range(reps):
+        lo, hi = r * nw, min(rows, (r + 1) * nw)
+        X[lo:hi] = feats[: hi - lo] + 1e-3 * r
+    out = {"trees": 500, "max_depth": 12, "forest_nodes": forest.total_nodes, "features": F, "rows": rows, "sweep": []}
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    for batch in (100_000, 1_000_000, 10_000_000, rows):
+        if batch > rows:
+            continue
+        raw = torch.empty((batch, 6), dtype=torch.float64, device="cuda"); prob = torch.empty_like(raw)
+        pred = torch.empty(batch, dtype=torch.float64, device="cuda")
+        nb = max(1, min(rows // batch, max(1, 20_000_000 // batch)))
+        forest.predict(X[:batch], is_forest=True)           # warm-up
+        a, b = ev(), ev()
+        a.record()
+        for i in range(nb):
+            forest.predict(X[i * batch:(i + 1) * batch], is_forest=True)
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / nb
+        out["sweep"].append({"batch_rows": batch, "ms_per_batch": ms, "rows_per_s": batch / (ms * 1e-3),
+                             "tree_rows_per_s": 500.0 * batch / (ms * 1e-3)})
+        del raw, prob, pred
+    best = max(out["sweep"], key=lambda r: r["rows_per_s"])
+    out["rows_per_s"] = best["rows_per_s"]
+    out["seconds_per_1e8_rows"] = 1e8 / best["rows_per_s"]
+    out["hbm_frac_at_448_B_per_row"] = best["rows_per_s"] * (F * 8 + 104) / 1e9 / float(measured_peaks()[0].get("hbm_gbs", 6650.0))
+    return out
 
 
 def main():

@@ -1057,6 +1057,15 @@ ORC_API int orc_num_threads(void) {
 #endif
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to its children; the timed CPU baseline sets its thread count explicitly */
+ORC_API void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* ---- raw WISDM text ingest (no reference code: the rules are those of
  * include/har_b200.h har_parse_wisdm_raw, restated with strtod / strtoll).  Returns the number of valid records
  * (written up to `capacity`), *dropped = malformed records. ------------------------------------------------------ */

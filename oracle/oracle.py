@@ -11,14 +11,41 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "_build", "libhar_oracle.so")
 _lib = None
 
 
+def _host_tag():
+    """The library is built -march=native, so its name carries the host CPU: a copy built on another machine
+    (the build box ships its tree to the GPU box) is not loaded there, it is rebuilt."""
+    import hashlib
+    model, flags = "", ""
+    try:
+        with open("/proc/cpuinfo") as fh:
+            for line in fh:
+                if line.startswith("model name") and not model:
+                    model = line.split(":", 1)[1].strip()
+                elif line.startswith("flags") and not flags:
+                    flags = line.split(":", 1)[1].strip()
+                if model and flags:
+                    break
+    except OSError:
+        pass
+    return hashlib.sha1((model + "|" + flags).encode()).hexdigest()[:12]
+
+
+_SO = os.path.join(_HERE, "_build", "libhar_oracle-%s.so" % _host_tag())
+CFLAGS = None
+
+
 def build(force=False):
+    global CFLAGS
     src = os.path.join(_HERE, "har_oracle.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
-        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    mk = os.path.join(_HERE, "Makefile")
+    stale = force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(src), os.path.getmtime(mk))
+    if stale:
+        subprocess.check_call(["make", "-C", _HERE, "-s", "OUT=" + os.path.relpath(_SO, _HERE)] + (["-B"] if force else []))
+    if CFLAGS is None:
+        CFLAGS = subprocess.run(["make", "-C", _HERE, "-s", "flags"], stdout=subprocess.PIPE, text=True).stdout.strip()
     return _SO
 
 
@@ -271,3 +298,7 @@ def parse_wisdm_raw(text, activities=WISDM_ACTIVITIES):
 
 def num_threads():
     return lib().orc_num_threads()
+
+
+def set_num_threads(n):
+    lib().orc_set_num_threads(C.c_int(int(n)))
