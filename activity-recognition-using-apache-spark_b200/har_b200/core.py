@@ -159,6 +159,25 @@ def window_features(x, y, z, ts, win_start, window_len=200, out=None):
     return out
 
 
+def window_transform(user, activity, ts, x, y, z, window_len=200, gap_ns=0):
+    """Segmentation + features in one library call (har_window_transform): -> (features [nw, 43] f64, win_user i32,
+    win_activity i32, win_start i64), views of buffers sized for n // window_len windows."""
+    require_cuda()
+    u, a, t = dev(user, np.int32), dev(activity, np.int32), dev(ts, np.int64)
+    xd, yd, zd = dev(x, np.float64), dev(y, np.float64), dev(z, np.float64)
+    n = u.numel()
+    cap = max(n // window_len, 1)
+    ws = torch.empty(cap, dtype=torch.int64, device="cuda")
+    wu = torch.empty(cap, dtype=torch.int32, device="cuda")
+    wa = torch.empty(cap, dtype=torch.int32, device="cuda")
+    out = torch.empty((cap, N.NUM_WINDOW_FEATURES), dtype=torch.float64, device="cuda")
+    nw = C.c_int64(0)
+    N.check(N.lib().har_window_transform(ptr(u), ptr(a), ptr(t), ptr(xd), ptr(yd), ptr(zd), n, window_len, gap_ns, ptr(ws),
+                                         ptr(wu), ptr(wa), ptr(out), N.NUM_WINDOW_FEATURES, C.byref(nw), stream()))
+    k = nw.value
+    return out[:k], wu[:k], wa[:k], ws[:k]
+
+
 # ---- tree stages -----------------------------------------------------------------------------------
 def resolve_features_per_node(strategy, F, num_trees):
     """DecisionTreeMetadata.buildMetadata's featureSubsetStrategy (classification), SURVEY A.5."""

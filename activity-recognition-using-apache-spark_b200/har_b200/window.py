@@ -55,9 +55,7 @@ class WisdmWindowFeaturizer(Transformer):
         u, a = core.dev(user, np.int32, pinned=True), core.dev(activity, np.int32, pinned=True)
         t = core.dev(ts, np.int64, pinned=True)
         xd, yd, zd = core.dev(x, np.float64, pinned=True), core.dev(y, np.float64, pinned=True), core.dev(z, np.float64, pinned=True)
-        ws, wu, wa = core.window_segments(u, a, t, window_len=L, gap_ns=self.getGapNs())
-        feats = core.window_features(xd, yd, zd, t, ws, window_len=L)
-        return feats, wu, wa, ws
+        return core.window_transform(u, a, t, xd, yd, zd, window_len=L, gap_ns=self.getGapNs())
 
     def _transform(self, dataset):
         c = dataset._cols

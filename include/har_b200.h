@@ -77,12 +77,12 @@ int har_window_segments(const int32_t* d_user, const int32_t* d_activity, const 
  * (or in Spark); it exists for hosts that are not allowed to allocate CUDA memory while running: a
  * process whose device memory is entirely owned by another allocator, a fixed-latency loop, a plug-in
  * sandbox limited to pre-approved buffers.  Same arguments and results as har_window_segments, but the
- * per-tile scratch lives in a HAR_SEGMENTS_STATIC_BYTES array built into the library (held by every GPU
+ * per-tile summaries live in a HAR_SEGMENTS_STATIC_BYTES array built into the library (held by every GPU
  * that loads it, for the life of the process) instead of coming from cudaMallocAsync, and the call
  * performs no cudaMalloc / cudaFree of any kind.
- *   - size limit: 256 + ceil(n / 2048) * (40 + 8 * (2048 / window_len + 1)) bytes must fit the array,
- *     i.e. 67,104,768 samples at window_len 200; larger inputs fail with HAR_E_UNSUPPORTED and a message
- *     that states the limit.
+ *   - size limit: 256 + ceil(n / 2048) * (28 + 2 * (2048 / window_len + 1), rounded up to a multiple of 4)
+ *     bytes must fit the array, i.e. 165,179,392 samples at window_len 200; larger inputs fail with
+ *     HAR_E_UNSUPPORTED and a message that states the limit.
  *   - the first call on each device looks the array's address up; make that call at start-up, before
  *     any stream capture.
  *   - all calls on a device share the array: calls that can overlap on the GPU race and must be
@@ -100,6 +100,16 @@ int har_window_segments_static(const int32_t* d_user, const int32_t* d_activity,
 int har_window_features(const double* d_x, const double* d_y, const double* d_z, const int64_t* d_ts,
                         int64_t n, const int64_t* d_win_start, int64_t num_windows, int32_t window_len,
                         double* d_out, int64_t ld_out, har_stream_t stream);
+
+/* a1 + a2 in one call: har_window_segments followed by har_window_features over the windows it found, queued back
+ * to back on `stream` (with window_len 200 the feature kernel reads the window count from device memory, so the host
+ * waits only once, for *num_windows).  d_win_start / d_win_user / d_win_activity (the latter two may be NULL) and
+ * d_out must have room for n / window_len windows; rows past *num_windows are left untouched.  Same definitions and
+ * limits as the two calls above.  No reference counterpart beyond theirs (wisdm_data.csv:1 is this call's output). */
+int har_window_transform(const int32_t* d_user, const int32_t* d_activity, const int64_t* d_ts,
+                         const double* d_x, const double* d_y, const double* d_z, int64_t n, int32_t window_len,
+                         int64_t gap_ns, int64_t* d_win_start, int32_t* d_win_user, int32_t* d_win_activity,
+                         double* d_out, int64_t ld_out, int64_t* num_windows, har_stream_t stream);
 
 /* Synthetic tri-axial stream of SURVEY §8(d) (bench / test input; counter-based so the CPU oracle
  * produces the same bits).  Bout table: host arrays, bout b covers global samples

@@ -112,3 +112,60 @@ def test_window_pipeline_properties_at_scale():
     sl = slice(k0, k0 + 50)
     want = orc.window_features(x.cpu().numpy(), y.cpu().numpy(), z.cpu().numpy(), ts.cpu().numpy(), ws[sl].cpu().numpy())
     np.testing.assert_allclose(np.nan_to_num(f[sl].cpu().numpy()), np.nan_to_num(want), rtol=RTOL, atol=0)
+
+
+@pytest.mark.parametrize("n,L", [(2048 * 100 + 77, 200), (2048 * 70, 64), (300_001, 2), (2048 * 40 + 5, 5000), (2047, 200), (700_001, 70_000)])
+def test_segments_long_bouts_span_many_tiles(n, L):
+    """One bout running over a hundred tiles (no boundary for the look-back to find for dozens of tiles), then a few
+    boundaries at awkward places: the windows of a bout open at a tile's start are placed in closed form."""
+    import torch
+    from har_b200 import core
+    u = np.zeros(n, np.int32); a = np.zeros(n, np.int32)
+    for cut in (n - 4097, n - 2049, n - 2048, n - 1):
+        if cut > 0:
+            a[cut:] += 1
+    ws, wu, wa = core.window_segments(torch.from_numpy(u).cuda(), torch.from_numpy(a).cuda(), None, window_len=L)
+    want = orc.window_segments(u, a, None, L=L)
+    assert np.array_equal(ws.cpu().numpy(), want) and len(want) >= n // L - 4
+    assert np.array_equal(wa.cpu().numpy(), a[want])
+
+
+def test_window_transform_equals_the_two_calls():
+    """har_window_transform (one call, window count taken from device memory) == segments then features."""
+    from har_b200 import core
+    for n, L in ((150_003, 200), (40_000, 50)):
+        u, a, ts, x, y, z = _gpu_stream(n, 5, 20000)
+        ws, wu, wa = core.window_segments(u, a, ts, window_len=L)
+        f = core.window_features(x, y, z, ts, ws, window_len=L)
+        f2, wu2, wa2, ws2 = core.window_transform(u, a, ts, x, y, z, window_len=L)
+        assert np.array_equal(ws.cpu().numpy(), ws2.cpu().numpy()) and np.array_equal(wu.cpu().numpy(), wu2.cpu().numpy())
+        assert np.array_equal(wa.cpu().numpy(), wa2.cpu().numpy())
+        assert np.array_equal(np.nan_to_num(f.cpu().numpy(), nan=-1.0).view(np.int64), np.nan_to_num(f2.cpu().numpy(), nan=-1.0).view(np.int64))
+
+
+def test_window_features_quantised_samples_with_ties():
+    """Readings with one decimal (the real WISDM files have two): plateaus, repeated maxima, windows whose largest
+    value sits on the first or last sample (then the highest PEAK is not the window maximum), equal peaks on the
+    threshold ladder.  Bins and peak intervals stay bit-exact."""
+    from har_b200 import core
+    n = 80_000
+    u, a, ts, x, y, z = _gpu_stream(n, 11, 20000)
+    xq = (x * 2).round() / 2
+    yq = y.round()
+    zq = (z * 10).round() / 10
+    ws, _, _ = core.window_segments(u, a, ts)
+    wsh = ws.cpu().numpy()
+    xh = xq.cpu().numpy().copy()
+    for k, w in enumerate(wsh[:40]):                 # plant the maximum on a window edge / a plateau at the start
+        if k % 4 == 0: xh[w] = 1e3
+        elif k % 4 == 1: xh[w + 199] = 1e3
+        elif k % 4 == 2: xh[w] = xh[w + 1] = 1e3
+        else: xh[w + 198] = xh[w + 199] = 1e3
+    import torch
+    xq = torch.from_numpy(xh).cuda()
+    got = core.window_features(xq, yq, zq, ts, ws).cpu().numpy()
+    want = orc.window_features(xh, yq.cpu().numpy(), zq.cpu().numpy(), ts.cpu().numpy(), wsh)
+    assert np.array_equal(got[:, :30], want[:, :30])
+    assert np.array_equal(np.nan_to_num(got[:, 33:36], nan=-1.0), np.nan_to_num(want[:, 33:36], nan=-1.0))
+    for cols in (slice(30, 33), slice(36, 43)):
+        np.testing.assert_allclose(got[:, cols], want[:, cols], rtol=RTOL, atol=0)
