@@ -78,21 +78,29 @@ __device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v)
 // ---------------------------------------------------------------------------------------------
 namespace {
 
-// scratch of one segmentation call: [0, 256) the window total, then the per-tile arrays of SegScratch
+// scratch of one segmentation call: [0, 256) the window total, then the hand-over words of the scan (two per slab of
+// 8192 tiles, at least 256 bytes), then the per-tile arrays of SegScratch
+size_t seg_header_bytes(int64_t num_tiles) {
+    const size_t chain = (size_t)har::ceil_div(std::max<int64_t>(num_tiles, 1), SEG_SCAN_SLAB) * 16;
+    return 256 + std::max<size_t>(256, (chain + 255) & ~(size_t)255);
+}
 size_t seg_scratch_bytes(int64_t num_tiles, int cap) {
-    return 256 + (size_t)num_tiles * seg_scratch_bytes_per_tile(cap);
+    return seg_header_bytes(num_tiles) + (size_t)num_tiles * seg_scratch_bytes_per_tile(cap);
 }
 
 // Launches the three segmentation kernels; *d_total (device) receives the window count.  Nothing is read back.
-// Every scratch entry a kernel reads is written earlier in the same call, so the scratch needs no clearing.
+// Of the scratch only the scan's hand-over words must start at zero (cleared here, on the stream); every other entry a
+// kernel reads is written earlier in the same call.
 int seg_launch(const int32_t* d_user, const int32_t* d_activity, const int64_t* d_ts, int64_t n, int32_t window_len,
                int64_t gap_ns, unsigned char* scratch, int64_t* d_win_start, int32_t* d_win_user, int32_t* d_win_activity,
                int64_t** d_total, cudaStream_t s) {
     const int64_t num_tiles = har::ceil_div(n, SEG_TILE);
     const int32_t cap = SEG_TILE / window_len + 1;
     SegScratch sc;
-    unsigned char* p = scratch + 256;
+    unsigned char* p = scratch + seg_header_bytes(num_tiles);
     sc.total = reinterpret_cast<int64_t*>(scratch);
+    sc.chain = reinterpret_cast<unsigned long long*>(scratch + 256);
+    HAR_CUDA(cudaMemsetAsync(scratch + 256, 0, seg_header_bytes(num_tiles) - 256, s));
     sc.summary = reinterpret_cast<unsigned long long*>(p); p += (size_t)num_tiles * 8;
     sc.open_bout = reinterpret_cast<int64_t*>(p); p += (size_t)num_tiles * 8;
     sc.out_base = reinterpret_cast<int64_t*>(p); p += (size_t)num_tiles * 8;
@@ -114,7 +122,7 @@ int seg_launch(const int32_t* d_user, const int32_t* d_activity, const int64_t* 
             HAR_CUDA(cudaFuncSetAttribute(k_seg_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             attr_set[dev] = true;                                   // idempotent
         }
-        k_seg_scan<<<1, SEG_SCAN_THREADS, smem, s>>>(sc, num_tiles, n, window_len, magic);
+        k_seg_scan<<<(unsigned)har::ceil_div(num_tiles, SEG_SCAN_SLAB), SEG_SCAN_THREADS, smem, s>>>(sc, num_tiles, n, window_len, magic);
     }
     HAR_LAUNCH_CHECK();
     k_seg_emit<<<(unsigned)har::ceil_div(num_tiles * 8, 256), 256, 0, s>>>(sc, cap, num_tiles, window_len, d_user, d_activity,
@@ -144,7 +152,7 @@ int features_launch(const double* d_x, const double* d_y, const double* d_z, con
         const size_t smem = W4_SMEM_PER_WARP * W4_WARPS;
         if (dev >= 0 && dev < 64 && !attr_set[dev]) {
             HAR_CUDA(cudaFuncSetAttribute(k_window_features_v4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            attr_set[dev] = true;                                   // idempotent: a racing second writer stores the same values
+            attr_set[dev] = true;                                   // idempotent: a racing second writer stores the same value
         }
         // bulk copies need 16-byte aligned columns (window starts are re-aligned to an even sample inside the kernel)
         const int tma_ok = ((reinterpret_cast<uintptr_t>(d_x) | reinterpret_cast<uintptr_t>(d_y) |
@@ -170,6 +178,25 @@ int features_launch(const double* d_x, const double* d_y, const double* d_z, con
     return HAR_OK;
 }
 
+// page-locked landing spot for the window count (per thread, allocated on first use; not used by the static entry point)
+int64_t* pinned_total() {
+    struct Holder { int64_t* p = nullptr; ~Holder() { if (p) cudaFreeHost(p); } };
+    static thread_local Holder h;
+    if (!h.p && cudaMallocHost((void**)&h.p, sizeof(int64_t)) != cudaSuccess) { cudaGetLastError(); h.p = nullptr; }
+    return h.p;
+}
+
+// device -> host copy of the count and the one wait of the call
+int read_total(const int64_t* d_total, int64_t* num_windows, cudaStream_t s) {
+    int64_t stack_total = 0;
+    int64_t* h = pinned_total();
+    if (!h) h = &stack_total;
+    HAR_CUDA(cudaMemcpyAsync(h, d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    HAR_CUDA(cudaStreamSynchronize(s));
+    *num_windows = *h;
+    return HAR_OK;
+}
+
 }  // namespace
 
 HAR_API int har_window_segments(const int32_t* d_user, const int32_t* d_activity, const int64_t* d_ts,
@@ -184,11 +211,7 @@ HAR_API int har_window_segments(const int32_t* d_user, const int32_t* d_activity
     int64_t* d_total = nullptr;
     if (int rc = seg_launch(d_user, d_activity, d_ts, n, window_len, gap_ns, scratch.p, d_win_start, d_win_user,
                             d_win_activity, &d_total, s)) return rc;
-    int64_t h_total = 0;
-    HAR_CUDA(cudaMemcpyAsync(&h_total, d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
-    HAR_CUDA(cudaStreamSynchronize(s));
-    *num_windows = h_total;
-    return HAR_OK;
+    return read_total(d_total, num_windows, s);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -211,10 +234,11 @@ HAR_API int har_window_segments(const int32_t* d_user, const int32_t* d_activity
 //
 // All calls on a device share the one array.  Two calls whose kernels can overlap on the GPU (different
 // streams, or different host threads) would overwrite each other's tile summaries: callers must
-// serialise them.  The array keeps whatever the previous call left in it; that is harmless here because
-// every entry a call reads (per-tile summary, open bout, output position, counts, the window list of each
-// tile up to its own count, and the total) is written earlier in the same call, so nothing has to be
-// cleared to zero beforehand.
+// serialise them.  The array keeps whatever the previous call left in it.  Only the few hand-over words
+// of the scan kernel must start at zero, and every call clears them itself (cudaMemsetAsync on the
+// caller's stream, which allocates nothing); every other entry a call reads (per-tile summary, first
+// window of the open bout, output position, counts, the window list of each tile up to its own count,
+// and the total) is written earlier in the same call.
 // ---------------------------------------------------------------------------------------------
 constexpr size_t SEG_STATIC_BYTES = 4u << 20;      // HAR_SEGMENTS_STATIC_BYTES
 static __device__ __align__(256) unsigned char g_seg_static[SEG_STATIC_BYTES];
@@ -246,7 +270,8 @@ HAR_API int har_window_segments_static(const int32_t* d_user, const int32_t* d_a
     const int32_t cap = SEG_TILE / window_len + 1;
     const size_t need = seg_scratch_bytes(num_tiles, cap);
     if (need > SEG_STATIC_BYTES) {
-        const long long max_n = (long long)((SEG_STATIC_BYTES - 256) / seg_scratch_bytes_per_tile(cap)) * SEG_TILE;
+        // (the array holds fewer than 2^17 tiles, so the header is 512 bytes)
+        const long long max_n = (long long)((SEG_STATIC_BYTES - 512) / seg_scratch_bytes_per_tile(cap)) * SEG_TILE;
         return har::fail(HAR_E_UNSUPPORTED,
                          "har_window_segments_static: %lld samples at window_len %d need %zu bytes of scratch but the "
                          "built-in array holds %zu; the limit at this window_len is %lld samples - use "
@@ -297,7 +322,6 @@ HAR_API int har_window_transform(const int32_t* d_user, const int32_t* d_activit
     const bool fused = window_len == W4_L;
     if (int rc = seg_launch(d_user, d_activity, d_ts, n, window_len, gap_ns, scratch.p, d_win_start, fused ? nullptr : d_win_user,
                             fused ? nullptr : d_win_activity, &d_total, s)) return rc;
-    int64_t h_total = 0;
     if (fused) {
         // the feature kernel takes the window count from device memory: the kernels are queued back to back and the
         // host waits once, for the count
@@ -305,14 +329,10 @@ HAR_API int har_window_transform(const int32_t* d_user, const int32_t* d_activit
         if (cap > 0)
             if (int rc = features_launch(d_x, d_y, d_z, d_ts, n, d_win_start, cap, d_total, window_len, d_out, ld_out, s,
                                          d_user, d_activity, d_win_user, d_win_activity)) return rc;
-        HAR_CUDA(cudaMemcpyAsync(&h_total, d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
-        HAR_CUDA(cudaStreamSynchronize(s));
-    } else {
-        HAR_CUDA(cudaMemcpyAsync(&h_total, d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
-        HAR_CUDA(cudaStreamSynchronize(s));
-        if (h_total > 0)
-            if (int rc = features_launch(d_x, d_y, d_z, d_ts, n, d_win_start, h_total, nullptr, window_len, d_out, ld_out, s)) return rc;
+        return read_total(d_total, num_windows, s);
     }
-    *num_windows = h_total;
+    if (int rc = read_total(d_total, num_windows, s)) return rc;
+    if (*num_windows > 0)
+        return features_launch(d_x, d_y, d_z, d_ts, n, d_win_start, *num_windows, nullptr, window_len, d_out, ld_out, s);
     return HAR_OK;
 }

@@ -30,6 +30,7 @@ struct SegScratch {                // carved from one allocation (or from the bu
     int32_t* npre;                 // [tiles]  windows of the open bout that end inside the tile
     uint16_t* local;               // [tiles][cap] tile-relative starts of the local windows
     int64_t* total;
+    unsigned long long* chain;     // [slabs of 8192 tiles][2] hand-over words of k_seg_scan; must start at zero
 };
 __host__ __device__ inline size_t seg_scratch_bytes_per_tile(int cap) { return 8 + 8 + 8 + 4 + (((size_t)cap * 2 + 3) & ~(size_t)3); }
 
@@ -169,14 +170,27 @@ k_seg_tiles(const int32_t* __restrict__ user, const int32_t* __restrict__ act, c
                            ((unsigned long long)(tile_last + 1) << 16) | ((unsigned long long)nlocal << 32);
 }
 
-// One CTA.  The summaries are brought into shared memory 8192 at a time with coalesced loads; every thread then
-// owns eight consecutive tiles of the slab, so the two block-wide scans (prefix maximum of the last boundaries,
-// prefix sum of the window counts) run once per slab, and the three per-tile results leave through shared memory too.
+// One CTA per slab of 8192 tile summaries, all slabs at once.  A slab is brought into shared memory with coalesced
+// loads; every thread owns eight consecutive tiles of it, so the two block-wide scans (prefix maximum of the last
+// boundaries, prefix sum of the window counts) run once, and the three per-tile results leave through shared memory
+// too.  What a slab needs from the slabs before it - the bout that is open at its start, and the number of windows
+// before it - travels along a chain of two 64-bit words per slab in global memory (0 = not published yet, the host
+// clears them): the first is published as soon as the slab knows its own last boundary, the second after its count.
+// CTAs are dispatched in index order, so a CTA only ever waits for CTAs that are running or done.
 constexpr int SEG_SCAN_THREADS = 1024;
 constexpr int SEG_SCAN_PER = 8;
 constexpr int SEG_SCAN_SLAB = SEG_SCAN_THREADS * SEG_SCAN_PER;
 constexpr int SEG_SCAN_PAD = SEG_SCAN_SLAB + SEG_SCAN_SLAB / 8;          // one pad element per thread's run: 72-byte lane stride
 __device__ __forceinline__ int seg_pad(int k) { return k + (k >> 3); }
+__device__ __forceinline__ unsigned long long seg_chain_wait(const unsigned long long* p) {
+    unsigned long long v;
+    do { asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory"); } while (v == 0);
+    return v;
+}
+__device__ __forceinline__ void seg_chain_post(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 __global__ void __launch_bounds__(SEG_SCAN_THREADS)
 k_seg_scan(SegScratch sc, int64_t num_tiles, int64_t n, int32_t L, unsigned magic) {
     extern __shared__ __align__(16) unsigned char seg_scan_smem[];
@@ -190,108 +204,130 @@ k_seg_scan(SegScratch sc, int64_t num_tiles, int64_t n, int32_t L, unsigned magi
     // (x / L, x % L) for x < L + 2048 by multiply-high while (L + 2048) * L < 2^32; plain division for longer windows
     const bool small_L = (unsigned long long)(uL + SEG_TILE) * uL < (1ULL << 32);
     auto udiv = [&](unsigned x) { return small_L ? __umulhi(x, magic) : x / uL; };
-    if (threadIdx.x == 0) { s_carry_b = -1; s_carry_n = 0; }
-    __syncthreads();
-    for (int64_t slab0 = 0; slab0 < num_tiles; slab0 += SEG_SCAN_SLAB) {
-        const int64_t in_slab = min((int64_t)SEG_SCAN_SLAB, num_tiles - slab0);
-        const int64_t slab_pos = slab0 * SEG_TILE;        // positions inside a slab fit 32 bits (8192 tiles x 2048 samples)
-        for (int k = threadIdx.x; k < SEG_SCAN_SLAB; k += SEG_SCAN_THREADS) s_sum[seg_pad(k)] = k < in_slab ? sc.summary[slab0 + k] : 0ULL;
-        __syncthreads();
-        const int64_t carry_b = s_carry_b, carry_n = s_carry_n;
-        const int k0 = threadIdx.x * SEG_SCAN_PER;
-        const int kp = seg_pad(k0);                       // this thread's eight entries are contiguous behind the pad
-        unsigned long long sv[SEG_SCAN_PER];
+    const int64_t slab = blockIdx.x;
+    const int64_t slab0 = slab * SEG_SCAN_SLAB;
+    const int64_t in_slab = min((int64_t)SEG_SCAN_SLAB, num_tiles - slab0);
+    const int64_t slab_pos = slab0 * SEG_TILE;            // positions inside a slab fit 32 bits (8192 tiles x 2048 samples)
+    unsigned long long* chain_b = sc.chain + 2 * slab;    // open bout after this slab, + 2 (1 = none)
+    unsigned long long* chain_n = chain_b + 1;            // windows up to the end of this slab, + 1
 #pragma unroll
-        for (int j = 0; j < SEG_SCAN_PER; j++) sv[j] = s_sum[kp + j];
-        // 1: last boundary inside this thread's tiles (slab-relative) -> exclusive prefix maximum over the threads
-        int mine = -1;
+    for (int i = 0; i < SEG_SCAN_PER; i++) {              // eight independent loads in flight per thread
+        const int k = threadIdx.x + i * SEG_SCAN_THREADS;
+        s_sum[seg_pad(k)] = k < in_slab ? sc.summary[slab0 + k] : 0ULL;
+    }
+    __syncthreads();
+    const int k0 = threadIdx.x * SEG_SCAN_PER;
+    const int kp = seg_pad(k0);                           // this thread's eight entries are contiguous behind the pad
+    unsigned long long sv[SEG_SCAN_PER];
+#pragma unroll
+    for (int j = 0; j < SEG_SCAN_PER; j++) sv[j] = s_sum[kp + j];
+    // 1: last boundary inside this thread's tiles (slab-relative) -> exclusive prefix maximum over the threads
+    int mine = -1;
+#pragma unroll
+    for (int j = 0; j < SEG_SCAN_PER; j++) {
+        const int lb = (int)((unsigned)(sv[j] >> 16) & 0xffffu);
+        if (lb) mine = (k0 + j) * SEG_TILE + lb - 1;
+    }
+    int incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) incl = max(incl, __shfl_up_sync(0xffffffffu, incl, d));
+    if (lane == 31) s_wlast[wid] = incl;
+    __syncthreads();
+    int wbase = -1;                                       // latest boundary in the warps before this one
+    {
+        int wi = s_wlast[lane];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) wi = max(wi, __shfl_up_sync(0xffffffffu, wi, d));
+        const int excl = __shfl_up_sync(0xffffffffu, wi, 1);
+        wbase = __shfl_sync(0xffffffffu, lane == 0 ? -1 : excl, wid);
+    }
+    if (wid == 0) {
+        int wi = s_wlast[lane];
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) wi = max(wi, __shfl_xor_sync(0xffffffffu, wi, d));
+        if (lane == 0) {
+            // what is open after this slab is its own last boundary (published at once), else whatever was open before it
+            if (wi >= 0) seg_chain_post(chain_b, (unsigned long long)(slab_pos + wi + 2));
+            const int64_t before = slab > 0 ? (int64_t)seg_chain_wait(chain_b - 2) - 2 : -1;
+            if (wi < 0) seg_chain_post(chain_b, (unsigned long long)(before + 2));
+            s_carry_b = before;
+        }
+    }
+    __syncthreads();
+    const int64_t carry_b = s_carry_b;
+    int open_rel = __shfl_up_sync(0xffffffffu, incl, 1);
+    if (lane == 0) open_rel = -1;
+    open_rel = max(open_rel, wbase);
+    const int64_t open = open_rel >= 0 ? slab_pos + open_rel : carry_b;
+    // 2: per tile, the first window of the open bout that ends inside the tile and how many of them do; count this
+    // thread's windows.  r = (tile start - bout start) mod L is carried from tile to tile, so the only 64-bit
+    // division is the one that starts the thread's run.
+    int total = 0;
+    {
+        const int64_t tb0 = slab_pos + (int64_t)k0 * SEG_TILE;
+        bool have = open >= 0;
+        unsigned r = have ? (unsigned)((tb0 - open) % L) : 0u;
 #pragma unroll
         for (int j = 0; j < SEG_SCAN_PER; j++) {
-            const int lb = (int)((unsigned)(sv[j] >> 16) & 0xffffu);
-            if (lb) mine = (k0 + j) * SEG_TILE + lb - 1;
+            const unsigned long long s = sv[j];
+            const unsigned fb = (unsigned)s & 0xffffu, lb = (unsigned)(s >> 16) & 0xffffu, nl = (unsigned)(s >> 32) & 0xffffu;
+            const int64_t tb = tb0 + (int64_t)j * SEG_TILE;
+            const unsigned span = fb ? fb - 1 : (unsigned)min((int64_t)SEG_TILE, n - tb);     // samples before the first boundary
+            const unsigned pre = (have && k0 + j < in_slab) ? udiv(r + span) : 0u;
+            s_out[kp + j] = tb - r;                        // start of the first such window
+            s_pre[kp + j] = (int)pre;
+            total += (int)(pre + nl);
+            const unsigned x = lb ? (unsigned)(SEG_TILE - (lb - 1)) : r + SEG_TILE;
+            have = have || lb != 0;
+            r = x - udiv(x) * uL;
         }
-        int incl = mine;
+    }
+    int cincl = total;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) incl = max(incl, __shfl_up_sync(0xffffffffu, incl, d));
-        if (lane == 31) s_wlast[wid] = incl;
-        __syncthreads();
-        int wbase = -1;                                   // latest boundary in the warps before this one
-        {
-            const int x = s_wlast[lane];
-            int wi = x;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) wi = max(wi, __shfl_up_sync(0xffffffffu, wi, d));
-            const int excl = __shfl_up_sync(0xffffffffu, wi, 1);
-            wbase = __shfl_sync(0xffffffffu, lane == 0 ? -1 : excl, wid);
-        }
-        int open_rel = __shfl_up_sync(0xffffffffu, incl, 1);
-        if (lane == 0) open_rel = -1;
-        open_rel = max(open_rel, wbase);
-        const int64_t open = open_rel >= 0 ? slab_pos + open_rel : carry_b;
-        // 2: per tile, the first window of the open bout that ends inside the tile and how many of them do; count this
-        // thread's windows.  r = (tile start - bout start) mod L is carried from tile to tile, so the only 64-bit
-        // division is the one that starts the thread's run.
-        int total = 0;
-        {
-            const int64_t tb0 = slab_pos + (int64_t)k0 * SEG_TILE;
-            bool have = open >= 0;
-            unsigned r = have ? (unsigned)((tb0 - open) % L) : 0u;
-#pragma unroll
-            for (int j = 0; j < SEG_SCAN_PER; j++) {
-                const unsigned long long s = sv[j];
-                const unsigned fb = (unsigned)s & 0xffffu, lb = (unsigned)(s >> 16) & 0xffffu, nl = (unsigned)(s >> 32) & 0xffffu;
-                const int64_t tb = tb0 + (int64_t)j * SEG_TILE;
-                const unsigned span = fb ? fb - 1 : (unsigned)min((int64_t)SEG_TILE, n - tb);     // samples before the first boundary
-                const unsigned pre = (have && k0 + j < in_slab) ? udiv(r + span) : 0u;
-                s_out[kp + j] = tb - r;                    // start of the first such window
-                s_pre[kp + j] = (int)pre;
-                total += (int)(pre + nl);
-                const unsigned x = lb ? (unsigned)(SEG_TILE - (lb - 1)) : r + SEG_TILE;
-                have = have || lb != 0;
-                r = x - udiv(x) * uL;
-            }
-        }
-        int cincl = total;
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, cincl, d);
+        if (lane >= d) cincl += o;
+    }
+    if (lane == 31) s_wcnt[wid] = cincl;
+    __syncthreads();
+    int woff = 0;
+    {
+        const int x = s_wcnt[lane];
+        int wi = x;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-            const int o = __shfl_up_sync(0xffffffffu, cincl, d);
-            if (lane >= d) cincl += o;
+            const int o = __shfl_up_sync(0xffffffffu, wi, d);
+            if (lane >= d) wi += o;
         }
-        if (lane == 31) s_wcnt[wid] = cincl;
-        __syncthreads();
-        int woff = 0, slab_total = 0;
-        {
-            const int x = s_wcnt[lane];
-            int wi = x;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int o = __shfl_up_sync(0xffffffffu, wi, d);
-                if (lane >= d) wi += o;
-            }
-            woff = __shfl_sync(0xffffffffu, wi - x, wid);
-            slab_total = __shfl_sync(0xffffffffu, wi, 31);
+        woff = __shfl_sync(0xffffffffu, wi - x, wid);
+        const int slab_total = __shfl_sync(0xffffffffu, wi, 31);
+        if (threadIdx.x == 0) {
+            const int64_t before = slab > 0 ? (int64_t)seg_chain_wait(chain_n - 2) - 1 : 0;
+            s_carry_n = before;
+            seg_chain_post(chain_n, (unsigned long long)(before + slab_total + 1));
+            if (slab == gridDim.x - 1) *sc.total = before + slab_total;
         }
-        int64_t off = carry_n + woff + cincl - total;
-        // first open-bout windows out (coalesced), then the output bases through the same buffer
-        for (int k = threadIdx.x; k < in_slab; k += SEG_SCAN_THREADS) { sc.open_bout[slab0 + k] = s_out[seg_pad(k)]; sc.npre[slab0 + k] = s_pre[seg_pad(k)]; }
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < SEG_SCAN_PER; j++) {
-            const unsigned nl = (unsigned)(sv[j] >> 32) & 0xffffu;
-            s_out[kp + j] = off;
-            off += s_pre[kp + j] + nl;
-        }
-        __syncthreads();
-        for (int k = threadIdx.x; k < in_slab; k += SEG_SCAN_THREADS) sc.out_base[slab0 + k] = s_out[seg_pad(k)];
-        if (threadIdx.x == SEG_SCAN_THREADS - 1) {
-            // the last thread's inclusive maximum covers the whole slab
-            const int all_last = max(incl, wbase);
-            s_carry_b = all_last >= 0 ? slab_pos + all_last : carry_b;
-            s_carry_n = carry_n + slab_total;
-        }
-        __syncthreads();
     }
-    if (threadIdx.x == 0) *sc.total = s_carry_n;
+    // first open-bout windows out (coalesced) while thread 0 may still be waiting for the count before this slab
+#pragma unroll
+    for (int i = 0; i < SEG_SCAN_PER; i++) {
+        const int k = threadIdx.x + i * SEG_SCAN_THREADS;
+        if (k < in_slab) { sc.open_bout[slab0 + k] = s_out[seg_pad(k)]; sc.npre[slab0 + k] = s_pre[seg_pad(k)]; }
+    }
+    __syncthreads();
+    int64_t off = s_carry_n + woff + cincl - total;
+#pragma unroll
+    for (int j = 0; j < SEG_SCAN_PER; j++) {
+        const unsigned nl = (unsigned)(sv[j] >> 32) & 0xffffu;
+        s_out[kp + j] = off;
+        off += s_pre[kp + j] + nl;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < SEG_SCAN_PER; i++) {
+        const int k = threadIdx.x + i * SEG_SCAN_THREADS;
+        if (k < in_slab) sc.out_base[slab0 + k] = s_out[seg_pad(k)];
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -350,6 +386,7 @@ __device__ __noinline__ double precise_sqrt_v4(double s) { return sqrt(s); }
         dst = _m;                                                                \
     }
 
+// (128 registers / 4 CTAs per SM was measured: the spills cost more than the extra warps bring, 1.30 vs 0.82 ms)
 __global__ void __launch_bounds__(W4_WARPS * 32, 3)
 k_window_features_v4(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ z,
                      const int64_t* __restrict__ ts, const int64_t* __restrict__ win_start,

@@ -80,13 +80,14 @@ int har_window_segments(const int32_t* d_user, const int32_t* d_activity, const 
  * per-tile summaries live in a HAR_SEGMENTS_STATIC_BYTES array built into the library (held by every GPU
  * that loads it, for the life of the process) instead of coming from cudaMallocAsync, and the call
  * performs no cudaMalloc / cudaFree of any kind.
- *   - size limit: 256 + ceil(n / 2048) * (28 + 2 * (2048 / window_len + 1), rounded up to a multiple of 4)
- *     bytes must fit the array, i.e. 165,179,392 samples at window_len 200; larger inputs fail with
+ *   - size limit: 512 + ceil(n / 2048) * (28 + 2 * (2048 / window_len + 1), rounded up to a multiple of 4)
+ *     bytes must fit the array, i.e. 165,169,152 samples at window_len 200; larger inputs fail with
  *     HAR_E_UNSUPPORTED and a message that states the limit.
  *   - the first call on each device looks the array's address up; make that call at start-up, before
  *     any stream capture.
  *   - all calls on a device share the array: calls that can overlap on the GPU race and must be
- *     serialised by the caller.  Stale contents from an earlier call are never read. */
+ *     serialised by the caller.  The few words that must start at zero are cleared by each call (on the stream,
+ *     without allocating); nothing else of an earlier call's contents is read. */
 #define HAR_SEGMENTS_STATIC_BYTES (4u << 20)
 int har_window_segments_static(const int32_t* d_user, const int32_t* d_activity, const int64_t* d_ts,
                                int64_t n, int32_t window_len, int64_t gap_ns,

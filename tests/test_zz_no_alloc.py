@@ -59,15 +59,15 @@ def test_static_segments_rejects_inputs_beyond_the_built_in_scratch():
     import torch
     from har_b200 import _native
     lib = _native.lib()
-    n = 170_000_000                                            # limit at window_len 200 is 165,179,392
+    n = 170_000_000                                            # limit at window_len 200 is 165,169,152
     user = torch.zeros(n, dtype=torch.int32, device="cuda")
     act = torch.zeros(n, dtype=torch.int32, device="cuda")
     rc, cnt, *_ = _call(lib.har_window_segments_static, user, act, None, 200)
     assert rc == _native_code("HAR_E_UNSUPPORTED") and cnt == 0
     msg = lib.har_last_error().decode()
-    assert "165179392" in msg and "har_window_segments" in msg
+    assert "165169152" in msg and "har_window_segments" in msg
     # just under the limit still works and agrees with the regular entry point
-    m = 165_179_392
+    m = 165_169_152
     rc2, cnt2, ws2, _, _ = _call(lib.har_window_segments_static, user[:m], act[:m], None, 200)
     rc3, cnt3, ws3, _, _ = _call(lib.har_window_segments, user[:m], act[:m], None, 200)
     assert rc2 == 0 and rc3 == 0 and cnt2 == cnt3 == m // 200 and np.array_equal(ws2, ws3)
