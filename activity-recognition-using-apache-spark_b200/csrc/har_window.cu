@@ -93,7 +93,7 @@ size_t seg_scratch_bytes(int64_t num_tiles, int cap) {
 // kernel reads is written earlier in the same call.
 int seg_launch(const int32_t* d_user, const int32_t* d_activity, const int64_t* d_ts, int64_t n, int32_t window_len,
                int64_t gap_ns, unsigned char* scratch, int64_t* d_win_start, int32_t* d_win_user, int32_t* d_win_activity,
-               int64_t** d_total, cudaStream_t s) {
+               int64_t** d_total, cudaStream_t s, cudaEvent_t after_scan = nullptr) {
     const int64_t num_tiles = har::ceil_div(n, SEG_TILE);
     const int32_t cap = SEG_TILE / window_len + 1;
     SegScratch sc;
@@ -125,6 +125,7 @@ int seg_launch(const int32_t* d_user, const int32_t* d_activity, const int64_t* 
         k_seg_scan<<<(unsigned)har::ceil_div(num_tiles, SEG_SCAN_SLAB), SEG_SCAN_THREADS, smem, s>>>(sc, num_tiles, n, window_len, magic);
     }
     HAR_LAUNCH_CHECK();
+    if (after_scan) HAR_CUDA(cudaEventRecord(after_scan, s));
     k_seg_emit<<<(unsigned)har::ceil_div(num_tiles * 8, 256), 256, 0, s>>>(sc, cap, num_tiles, window_len, d_user, d_activity,
                                                                           d_win_start, d_win_user, d_win_activity);
     HAR_LAUNCH_CHECK();
@@ -185,6 +186,34 @@ int64_t* pinned_total() {
     if (!h.p && cudaMallocHost((void**)&h.p, sizeof(int64_t)) != cudaSuccess) { cudaGetLastError(); h.p = nullptr; }
     return h.p;
 }
+
+// The fused call hands the count to the host while the feature kernel is still running: a side stream waits for the
+// scan (event), copies the count into page-locked memory, and the host waits for that copy only.
+struct CountLane {
+    cudaStream_t side = nullptr;
+    cudaEvent_t scanned = nullptr, copied = nullptr;
+    int dev = -1;
+    ~CountLane() { reset(); }
+    void reset() {
+        if (scanned) cudaEventDestroy(scanned);
+        if (copied) cudaEventDestroy(copied);
+        if (side) cudaStreamDestroy(side);
+        side = nullptr; scanned = copied = nullptr; dev = -1;
+    }
+    cudaError_t ensure() {
+        int cur = 0;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (side && dev == cur) return cudaSuccess;
+        reset();
+        if ((e = cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&scanned, cudaEventDisableTiming)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&copied, cudaEventDisableTiming)) != cudaSuccess) return e;
+        dev = cur;
+        return cudaSuccess;
+    }
+};
+CountLane& count_lane() { static thread_local CountLane c; return c; }
 
 // device -> host copy of the count and the one wait of the call
 int read_total(const int64_t* d_total, int64_t* num_windows, cudaStream_t s) {
@@ -320,16 +349,27 @@ HAR_API int har_window_transform(const int32_t* d_user, const int32_t* d_activit
     // with window_len 200 the feature kernel also fills win_user / win_activity (it has every window's start at hand):
     // the emit pass then writes the window starts only
     const bool fused = window_len == W4_L;
+    int64_t* h_total = fused ? pinned_total() : nullptr;
+    CountLane& lane = count_lane();
+    const bool early = fused && h_total && lane.ensure() == cudaSuccess;
     if (int rc = seg_launch(d_user, d_activity, d_ts, n, window_len, gap_ns, scratch.p, d_win_start, fused ? nullptr : d_win_user,
-                            fused ? nullptr : d_win_activity, &d_total, s)) return rc;
+                            fused ? nullptr : d_win_activity, &d_total, s, early ? lane.scanned : nullptr)) return rc;
     if (fused) {
-        // the feature kernel takes the window count from device memory: the kernels are queued back to back and the
-        // host waits once, for the count
+        // the feature kernel takes the window count from device memory: the kernels are queued back to back
         const int64_t cap = n / window_len;
         if (cap > 0)
             if (int rc = features_launch(d_x, d_y, d_z, d_ts, n, d_win_start, cap, d_total, window_len, d_out, ld_out, s,
                                          d_user, d_activity, d_win_user, d_win_activity)) return rc;
-        return read_total(d_total, num_windows, s);
+        if (!early) return read_total(d_total, num_windows, s);
+        // the count is ready as soon as the scan is: copy it on the side stream and wait for that copy only (the
+        // feature kernel keeps running; `stream` must not free the scratch before it ends, hence the join below)
+        HAR_CUDA(cudaStreamWaitEvent(lane.side, lane.scanned, 0));
+        HAR_CUDA(cudaMemcpyAsync(h_total, d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, lane.side));
+        HAR_CUDA(cudaEventRecord(lane.copied, lane.side));
+        HAR_CUDA(cudaStreamWaitEvent(s, lane.copied, 0));
+        HAR_CUDA(cudaEventSynchronize(lane.copied));
+        *num_windows = *h_total;
+        return HAR_OK;
     }
     if (int rc = read_total(d_total, num_windows, s)) return rc;
     if (*num_windows > 0)

@@ -499,6 +499,7 @@ k_window_features_v4(const double* __restrict__ x, const double* __restrict__ y,
         const double nxt = __shfl_down_sync(0xffffffffu, v[0], 1);       // first sample of the next lane
         unsigned up = 0;
         double sum0 = 0.0, sum1 = 0.0, hi = v[24], lo = v[24];
+        int hpair = 12;                                            // pair that holds this lane's maximum (12: the last sample)
 #pragma unroll
         for (int j = 0; j < W4_PER_LANE; j++) {
             const double r = j + 1 < W4_PER_LANE ? v[j + 1] : nxt;
@@ -506,13 +507,15 @@ k_window_features_v4(const double* __restrict__ x, const double* __restrict__ y,
             up |= (g ? 1u : 0u) << j;
             if ((j & 1) == 0 && j + 1 < W4_PER_LANE) {           // one compare orders the pair: larger to hi, smaller to lo
                 const double pmx = g ? r : v[j], pmn = g ? v[j] : r;
-                hi = pmx > hi ? pmx : hi;
+                const bool nh = pmx > hi;
+                hi = nh ? pmx : hi;
+                hpair = nh ? (j >> 1) : hpair;
                 lo = pmn < lo ? pmn : lo;
             }
             if (j & 1) sum1 += v[j]; else sum0 += v[j];
-            r2[j] = fma(v[j], v[j], r2[j]);
         }
         double sum = sum0 + sum1;
+        const double lane_hi = hi;
         const unsigned up_prev = __shfl_up_sync(0xffffffffu, up, 1);
         unsigned pk = ((up << 1) | (sub ? (up_prev >> 24) & 1u : 0u)) & ~up & 0x1ffffffu;
         if (sub == 0) pk &= ~1u;                                   // first sample of the window
@@ -524,12 +527,20 @@ k_window_features_v4(const double* __restrict__ x, const double* __restrict__ y,
             lo = ol < lo ? ol : lo;
             hi = oh > hi ? oh : hi;
         }
+        // work that does not need the window-wide sum / minimum / maximum sits here, behind the shuffles above and
+        // under the division below: the squares for RESULTANT and the test "is the maximum one of the peaks"
+#pragma unroll
+        for (int j = 0; j < W4_PER_LANE; j++) r2[j] = fma(v[j], v[j], r2[j]);
         const double mean = sum * 0.005;                           // within an ulp of sum / 200 (AVG is compared to 1e-6)
         const double scale = hi > lo ? 10.0 / (hi - lo) : 0.0;     // exact: decides the bins
+        // "the window maximum is one of the peaks": looked up at one place per lane, the sample that gave the lane its
+        // maximum.  A yes is always right; a no can be wrong when the maximum occurs twice in a lane (the exact search
+        // below then finds it anyway).
+        const int hpos = hpair < 12 ? 2 * hpair + (int)((up >> (2 * hpair)) & 1u) : 24;
+        const bool lane_top = lane_hi == hi && ((pk >> hpos) & 1u);
 
         // ---- deviations and the 10-bin counts (5-bit fields of one double: exact below 2^53) ----
         double sq = 0.0, sq1 = 0.0, ab = 0.0, ab1 = 0.0, packed = 0.0, packed1 = 0.0;
-        unsigned eqhi = 0;
 #pragma unroll
         for (int j = 0; j < W4_PER_LANE; j++) {
             const double d = v[j] - mean;
@@ -538,7 +549,6 @@ k_window_features_v4(const double* __restrict__ x, const double* __restrict__ y,
             const double one = __hiloint2double((1023 + 5 * bq) << 20, 0);                 // 2^(5 * bin)
             if (j & 1) { sq1 = fma(d, d, sq1); ab1 += fabs(d); packed1 += one; }
             else { sq = fma(d, d, sq); ab += fabs(d); packed += one; }
-            eqhi |= (v[j] == hi ? 1u : 0u) << j;
         }
         sq += sq1; ab += ab1; packed += packed1;
         int npk = __popc(pk);
@@ -547,7 +557,7 @@ k_window_features_v4(const double* __restrict__ x, const double* __restrict__ y,
         const unsigned F3 = 0x1fu | (0x1fu << 10) | (0x1fu << 20);
         unsigned b024 = (unsigned)pbits & F3, b135 = (unsigned)(pbits >> 5) & F3;
         unsigned b68 = (unsigned)(pbits >> 30) & F3, b79 = (unsigned)(pbits >> 35) & F3;
-        int top_is_peak = (eqhi & pk) != 0;
+        int top_is_peak = lane_top ? 1 : 0;
 #pragma unroll
         for (int m = 4; m >= 1; m >>= 1) {
             sq += shfl_xor_d(sq, m);
@@ -640,18 +650,20 @@ k_window_features_v4(const double* __restrict__ x, const double* __restrict__ y,
         }
         // ---- RESULTANT after the third axis: sqrt by the fp64 rsqrt seed + one Newton step (rel. error < 1e-13) ----
         if (a == 2) {
-            double rs = 0.0;
-            bool odd = false;
+            double rs = 0.0, rs1 = 0.0;
 #pragma unroll
             for (int j = 0; j < W4_PER_LANE; j++) {
                 const double s2 = r2[j];
                 const double r = rsqrt_approx_f64(s2);
                 double yv = s2 * r;
                 yv = fma(0.5 * r, fma(-yv, yv, s2), yv);
-                odd = odd || !(s2 > 1e-280 && s2 < 1e280);
-                rs += yv;
+                if (j & 1) rs1 += yv; else rs += yv;
             }
-            if (__any_sync(0xffffffffu, odd)) {                    // zeros, denormals, infinities: the library sqrt
+            rs += rs1;
+            // a zero or denormal square (seed +inf) or an infinite one (seed 0) turns its term into NaN, huge ones overflow:
+            // one test on the sum catches them all
+            const bool odd = !(rs < 1e300);
+            if (__any_sync(0xffffffffu, odd)) {                    // the library sqrt
                 rs = 0.0;
 #pragma unroll
                 for (int j = 0; j < W4_PER_LANE; j++) rs += precise_sqrt_v4(r2[j]);

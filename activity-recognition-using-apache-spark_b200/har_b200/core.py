@@ -167,9 +167,10 @@ def window_transform(user, activity, ts, x, y, z, window_len=200, gap_ns=0):
     xd, yd, zd = dev(x, np.float64), dev(y, np.float64), dev(z, np.float64)
     n = u.numel()
     cap = max(n // window_len, 1)
-    ws = torch.empty(cap, dtype=torch.int64, device="cuda")
-    wu = torch.empty(cap, dtype=torch.int32, device="cuda")
-    wa = torch.empty(cap, dtype=torch.int32, device="cuda")
+    meta = torch.empty(2 * cap, dtype=torch.int64, device="cuda")           # window starts | users, activities (one allocation)
+    ws = meta[:cap]
+    ua = meta[cap:].view(torch.int32)
+    wu, wa = ua[:cap], ua[cap:]
     out = torch.empty((cap, N.NUM_WINDOW_FEATURES), dtype=torch.float64, device="cuda")
     nw = C.c_int64(0)
     N.check(N.lib().har_window_transform(ptr(u), ptr(a), ptr(t), ptr(xd), ptr(yd), ptr(zd), n, window_len, gap_ns, ptr(ws),

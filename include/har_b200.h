@@ -103,10 +103,12 @@ int har_window_features(const double* d_x, const double* d_y, const double* d_z,
                         double* d_out, int64_t ld_out, har_stream_t stream);
 
 /* a1 + a2 in one call: har_window_segments followed by har_window_features over the windows it found, queued back
- * to back on `stream` (with window_len 200 the feature kernel reads the window count from device memory, so the host
- * waits only once, for *num_windows).  d_win_start / d_win_user / d_win_activity (the latter two may be NULL) and
- * d_out must have room for n / window_len windows; rows past *num_windows are left untouched.  Same definitions and
- * limits as the two calls above.  No reference counterpart beyond theirs (wisdm_data.csv:1 is this call's output). */
+ * to back on `stream`.  With window_len 200 the feature kernel reads the window count from device memory and fills
+ * d_win_user / d_win_activity itself, and the call returns as soon as the count has reached the host: *num_windows is
+ * valid on return, the device outputs are complete in stream order (as with har_window_features).  d_win_start /
+ * d_win_user / d_win_activity (the latter two may be NULL) and d_out must have room for n / window_len windows; rows
+ * past *num_windows are left untouched.  Same definitions and limits as the two calls above.  No reference
+ * counterpart beyond theirs (wisdm_data.csv:1 is this call's output). */
 int har_window_transform(const int32_t* d_user, const int32_t* d_activity, const int64_t* d_ts,
                          const double* d_x, const double* d_y, const double* d_z, int64_t n, int32_t window_len,
                          int64_t gap_ns, int64_t* d_win_start, int32_t* d_win_user, int32_t* d_win_activity,
