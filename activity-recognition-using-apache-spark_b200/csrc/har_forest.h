@@ -36,6 +36,18 @@ struct har_forest {
     int64_t total_nodes = -1;     // pruned node count, known before the host arrays exist
     mutable std::function<int()> materialize;
     int max_depth = 0;
+    // binned predict path (har_predict.cu): compact nodes + category masks converted from d_nodes, and the device
+    // copies of the split candidates the rows are binned with.  binnable: -1 not decided, 0 no (imported forest, a
+    // threshold that is not a candidate, too many features), 1 yes.
+    void* d_cnodes = nullptr;            // CNode[num compact]
+    unsigned long long* d_cmask = nullptr;
+    double* d_bin_thr = nullptr;         // [F][max_bins]
+    int32_t* d_bin_ns = nullptr;         // [F]
+    void* d_walk = nullptr;              // uint2[num compact]: branch-free walk table (no categorical nodes)
+    uint32_t* d_leaf_of = nullptr;       // [num compact] leaf-vector index of a leaf node
+    bool has_cat_nodes = false;
+    int64_t num_cnodes = 0;
+    int binnable = -1;
 };
 
 // Fill the flat host arrays if the fit left them on the device.  Returns 0 (HAR_OK) or the error of the read-back.

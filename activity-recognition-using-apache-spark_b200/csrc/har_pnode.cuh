@@ -27,6 +27,19 @@ __host__ __device__ inline void pnode_set_categorical(PNode& d, int32_t feature,
     else { d.mask = (left_mask & dom) | ~dom; d.feature |= P_DEFLEFT; }
 }
 
+// Compact node of the binned predict path: 8 bytes, so that the 4095 nodes of a depth-12 tree are 32 KB and the trees
+// being walked stay in L1.  Rows are binned first (u8 per feature, TreePoint.findBin), and `x[f] <= threshold` becomes
+// `bin[f] <= split` - every threshold of a fitted forest is one of the feature's candidate thresholds.  Categorical
+// nodes keep their 64-bit mask in a side table indexed like the nodes.
+struct __align__(8) CNode {
+    uint16_t feature;    // leaf: unused
+    uint8_t split;       // continuous: index of the threshold among the feature's candidates
+    uint8_t flags;       // C_LEAF | C_CAT | C_DEFLEFT
+    uint32_t left;       // internal: index of the left child (right = left + 1); leaf: leaf-vector index
+};
+constexpr uint8_t C_LEAF = 1, C_CAT = 2, C_DEFLEFT = 4;
+constexpr uint8_t BIN_OUTSIDE = 255;   // categorical value outside [0, 64) or not an integer
+
 // leaf vectors of the predict kernel from per-slot class counts: DT = counts, RF = counts / total
 static __global__ void k_fin_leaf_table(const uint32_t* __restrict__ slot_stats, int64_t nslots, int C, int is_forest, double* __restrict__ leaf) {
     const int64_t sidx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

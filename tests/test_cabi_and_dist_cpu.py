@@ -164,3 +164,25 @@ def test_bench_reference_arm_prints_the_contract_line():
     out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1"], env=env,
                          stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
     assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+def test_forest_import_rejects_malformed_models():
+    """har_forest_import validates the flat arrays on the host (no GPU needed): a truncated or cyclic model must not
+    reach the predict kernel."""
+    from har_b200 import core
+    from har_b200._native import HarError
+    ok = dict(tree_off=[0, 3], feature=[0, -1, -1], left=[1, -1, -1], right=[2, -1, -1], arity=[0, 0, 0],
+              threshold=[0.5, 0, 0], left_mask=[0, 0, 0], stats=np.ones((3, 2)))
+    f = core.Forest.from_arrays(1, 2, 1, **ok)
+    assert f.total_nodes == 3
+    for field, value, msg in (("left", [2, -1, -1], "two parents"), ("right", [5, -1, -1], "child outside"),
+                              ("left", [0, -1, -1], "child outside"), ("feature", [3, -1, -1], "tests feature"),
+                              ("arity", [70, 0, 0], "arity"), ("tree_off", [0, 0], "empty")):
+        bad = dict(ok); bad[field] = value
+        with pytest.raises(HarError, match=msg):
+            core.Forest.from_arrays(1, 2, 1, **bad)
+    # a node that nothing points to
+    bad = dict(ok, tree_off=[0, 4], feature=[0, -1, -1, -1], left=[1, -1, -1, -1], right=[2, -1, -1, -1], arity=[0] * 4,
+               threshold=[0.5, 0, 0, 0], left_mask=[0] * 4, stats=np.ones((4, 2)))
+    with pytest.raises(HarError, match="not reachable"):
+        core.Forest.from_arrays(1, 2, 1, **bad)

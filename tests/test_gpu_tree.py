@@ -356,3 +356,43 @@ def test_main_py_random_forest_section_in_reference_band(wisdm, golden):
     assert abs(model.featureImportances.toArray().sum() - 1.0) < 1e-9
     one = model.trees[3].transform(test)
     assert one.count() == test.count()
+
+
+def test_binned_predict_equals_the_f64_walk_at_the_edges(monkeypatch):
+    """Fitted forests are scored on binned rows (x <= threshold  <=>  bin(x) <= split index).  Inputs that sit exactly on
+    thresholds, signed zeros, NaN, infinities and out-of-domain categories must give the bits of the f64 walk
+    (HAR_PREDICT_BINS=0) and of the oracle, in both predict modes; an imported forest (no split candidates) keeps the
+    f64 walk."""
+    from har_b200 import core
+    X, y, arity = synth_tree_data(12000, F=10, C=4, seed=61, n_cat_unordered=1, n_cat_ordered=1, quantize=4)
+    X[::5, 3] = 0.0; X[1::5, 3] = -0.0
+    kw = dict(arity=arity, num_classes=4, num_trees=9, max_depth=9, feature_subset="all", seed=5)
+    g = core.fit_forest(X, y, **kw)
+    rng = np.random.RandomState(9)
+    Xt = rng.randn(30000, 10)
+    Xt[:, 0] = rng.randint(-1, 6, 30000); Xt[:, 1] = rng.randint(0, 9, 30000)          # category -1, 4, 5 are outside arity 4
+    thr = g.thresholds
+    for f in range(2, 10):                                                              # exact threshold hits and neighbours
+        ns = int(g.nsplits[f])
+        if ns:
+            pick = thr[f, rng.randint(0, ns, 30000)]
+            Xt[::3, f] = pick[::3]
+            Xt[1::9, f] = np.nextafter(pick[1::9], np.inf)
+            Xt[2::9, f] = np.nextafter(pick[2::9], -np.inf)
+    Xt[7::101, 4] = np.nan; Xt[8::101, 5] = np.inf; Xt[9::101, 6] = -np.inf; Xt[10::101, 3] = -0.0; Xt[11::101, 3] = 0.0
+    Xt[12::101, 0] = 2.5                                                                 # non-integral category
+    got = {m: [t.cpu().numpy() for t in g.predict(Xt, is_forest=m)] for m in (True, False)}
+    o = orc.fit_forest(X, y, **kw)
+    ro, po_, pr = orc.predict(o, Xt, is_forest=True)
+    assert np.array_equal(_bits(got[True][0]), _bits(ro)) and np.array_equal(_bits(got[True][1]), _bits(po_)) and np.array_equal(got[True][2], pr)
+    monkeypatch.setenv("HAR_PREDICT_BINS", "0")
+    g2 = core.fit_forest(X, y, **kw)
+    for m in (True, False):
+        ref = [t.cpu().numpy() for t in g2.predict(Xt, is_forest=m)]
+        for a, b in zip(ref, got[m]):
+            assert np.array_equal(_bits(a), _bits(b))
+    monkeypatch.delenv("HAR_PREDICT_BINS")
+    imp = core.Forest.from_arrays(g.T, g.C, g.F, g.tree_off, g.feature, g.left, g.right, g.arity, g.threshold, g.left_mask, g.stats)
+    ri = [t.cpu().numpy() for t in imp.predict(Xt, is_forest=True)]
+    for a, b in zip(ri, got[True]):
+        assert np.array_equal(_bits(a), _bits(b))
