@@ -189,21 +189,21 @@ bool dist_has_nccl(const har_dist* d, cudaStream_t s) {
     return get_comm(d, s, &comm) == HAR_OK && comm != nullptr;
 }
 
-// Sum of the int32 segment [off[r], off[r+1]) of `buf` lands on rank r (in place); the other segments are left with
-// partial sums.  One ncclReduce per rank inside a group call: segments are whole nodes, so their sizes differ.
-int dist_reduce_segments(const har_dist* d, int32_t* buf, const int64_t* off, cudaStream_t s) {
+// Node-sharded exchange (NCCL only).  reduce: every op sums `cnt[k]` int32 at `ptr[k]` over all ranks onto rank
+// `root[k]` (in place; the other ranks keep partial sums).  bcast: every op sends `bytes[k]` bytes at `ptr[k]` from rank
+// `root[k]` to everybody (in place).  All ops of a call travel in one NCCL group; empty ops are skipped.
+int dist_reduce_list(const har_dist* d, int n_ops, int32_t* const* ptr, const int64_t* cnt, const int* root, cudaStream_t s) {
     if (!d || d->world_size <= 1) return HAR_OK;
     void* comm = nullptr;
     if (int rc = get_comm(d, s, &comm)) return rc;
-    if (!comm) return fail(HAR_E_COMM, "dist_reduce_segments needs the library's NCCL communicator");
+    if (!comm) return fail(HAR_E_COMM, "dist_reduce_list needs the library's NCCL communicator");
     NcclApi& api = nccl();
     g_calls += 1;
     int rc = api.group_start();
-    for (int r = 0; r < d->world_size && rc == 0; r++) {
-        const int64_t cnt = off[r + 1] - off[r];
-        if (cnt <= 0) continue;
-        g_bytes += 4 * cnt;
-        rc = api.reduce(buf + off[r], buf + off[r], (size_t)cnt, kNcclInt32, kNcclSum, r, comm, s);
+    for (int k = 0; k < n_ops && rc == 0; k++) {
+        if (cnt[k] <= 0) continue;
+        g_bytes += 4 * cnt[k];
+        rc = api.reduce(ptr[k], ptr[k], (size_t)cnt[k], kNcclInt32, kNcclSum, root[k], comm, s);
     }
     int rc2 = api.group_end();
     if (rc == 0) rc = rc2;
@@ -211,22 +211,18 @@ int dist_reduce_segments(const har_dist* d, int32_t* buf, const int64_t* off, cu
     return HAR_OK;
 }
 
-// Byte segment [off[r], off[r+1]) of `buf` is sent from rank r to everybody (in place): the all-gather of the
-// per-node results, with uneven segment sizes.
-int dist_gather_segments(const har_dist* d, void* buf, const int64_t* off, cudaStream_t s) {
+int dist_bcast_list(const har_dist* d, int n_ops, void* const* ptr, const int64_t* bytes, const int* root, cudaStream_t s) {
     if (!d || d->world_size <= 1) return HAR_OK;
     void* comm = nullptr;
     if (int rc = get_comm(d, s, &comm)) return rc;
-    if (!comm) return fail(HAR_E_COMM, "dist_gather_segments needs the library's NCCL communicator");
+    if (!comm) return fail(HAR_E_COMM, "dist_bcast_list needs the library's NCCL communicator");
     NcclApi& api = nccl();
     g_calls += 1;
     int rc = api.group_start();
-    for (int r = 0; r < d->world_size && rc == 0; r++) {
-        const int64_t cnt = off[r + 1] - off[r];
-        if (cnt <= 0) continue;
-        g_bytes += cnt;
-        char* p = static_cast<char*>(buf) + off[r];
-        rc = api.bcast(p, p, (size_t)cnt, kNcclInt8, r, comm, s);
+    for (int k = 0; k < n_ops && rc == 0; k++) {
+        if (bytes[k] <= 0) continue;
+        g_bytes += bytes[k];
+        rc = api.bcast(ptr[k], ptr[k], (size_t)bytes[k], kNcclInt8, root[k], comm, s);
     }
     int rc2 = api.group_end();
     if (rc == 0) rc = rc2;

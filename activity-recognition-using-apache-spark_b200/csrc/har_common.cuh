@@ -28,9 +28,9 @@ void reset_launches();
 int dist_allreduce(const har_dist* d, void* buf, int64_t count, cudaStream_t s);
 // true when the group's exchanges run on the library's own NCCL communicator (collective on first use)
 bool dist_has_nccl(const har_dist* d, cudaStream_t s);
-// node-sharded exchange (NCCL only): sum of int32 segment r lands on rank r / byte segment r goes from rank r to all
-int dist_reduce_segments(const har_dist* d, int32_t* buf, const int64_t* off, cudaStream_t s);
-int dist_gather_segments(const har_dist* d, void* buf, const int64_t* off, cudaStream_t s);
+// node-sharded exchange (NCCL only): sums of int32 runs onto their owners / owners' byte runs to everybody, one group each
+int dist_reduce_list(const har_dist* d, int n_ops, int32_t* const* ptr, const int64_t* cnt, const int* root, cudaStream_t s);
+int dist_bcast_list(const har_dist* d, int n_ops, void* const* ptr, const int64_t* bytes, const int* root, cudaStream_t s);
 
 // optional CUDA-event timing of selected kernels (har_debug_profile_*; off by default)
 enum ProfId { PROF_NODE_HIST = 0, PROF_BEST_SPLIT, PROF_PART_COUNT, PROF_PART_SCATTER, PROF_WINDOW_FEATURES,

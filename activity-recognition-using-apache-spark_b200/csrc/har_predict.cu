@@ -379,7 +379,9 @@ void free_device_tables(har_forest* f) {
 // f->binnable; 0 means "use the f64 walk" and is not an error.
 int build_compact_tables(har_forest* f, cudaStream_t s) {
     if (f->binnable >= 0) return HAR_OK;
-    static const bool off = [] { const char* e = std::getenv("HAR_PREDICT_BINS"); return e && std::atoi(e) == 0; }();
+    // HAR_PREDICT_BINS=0 (read when a forest's tables are built, so tests can flip it per forest) keeps the f64 walk
+    const char* env_bins = std::getenv("HAR_PREDICT_BINS");
+    const bool off = env_bins && std::atoi(env_bins) == 0;
     const int64_t np = f->d_slot_stats ? f->num_slots : (int64_t)f->feature.size();
     const int bstride = 4 * (((f->F + 3) >> 2) | 1);           // bytes per staged row: a multiple of 4 with an odd word count
     if (off || f->nsplits.empty() || f->max_bins < 2 || f->max_bins > 256 || f->F >= 65535 || np <= 0 || np >= (1LL << 32) ||

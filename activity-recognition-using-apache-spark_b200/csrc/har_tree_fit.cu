@@ -205,17 +205,15 @@ int bin_features_impl(const double* d_X, int64_t n, int F, int64_t ld, const int
 // BaggedPoint.convertToBaggedRDD: Poisson(rate) with replacement when numTrees > 1, else Bernoulli(rate)
 int launch_bag(int64_t n, int T, double rate, int64_t seed, const int64_t* d_part_off, int num_parts, int partition_offset,
                uint8_t* d_w, cudaStream_t s) {
-    static const bool v1 = [] { const char* e = std::getenv("HAR_BAG_KERNEL"); return e && std::string(e) == "v1"; }();
     const unsigned grid = (unsigned)ceil_div(num_parts, 32);
-    if (T > 1 && !v1) {
+    if (T > 1) {
         const double lim = std::ceil(1000.0 * rate);
         const int ilimit = lim >= 2147483647.0 ? 2147483647 : (int)lim;
         const size_t smem = BAG_SMEM_BYTES;
         HAR_CUDA(cudaFuncSetAttribute(k_bag_poisson, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_bag_poisson<<<grid, BAG_THREADS, smem, s>>>(n, T, std::exp(-rate), ilimit, seed, d_part_off, num_parts, partition_offset, d_w);
     } else {
-        k_bag_weights<<<grid, 32, 0, s>>>(n, T, rate, std::exp(-rate), seed, d_part_off, num_parts, partition_offset,
-                                          T > 1 ? 1 : 0, d_w);
+        k_bag_weights<<<grid, 32, 0, s>>>(n, T, rate, seed, d_part_off, num_parts, partition_offset, d_w);
     }
     HAR_LAUNCH_CHECK();
     return HAR_OK;
@@ -857,7 +855,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     struct PinnedScratch {
         Pinned<NodeDesc> h_nodes; Pinned<NodeResult> h_res; Pinned<uint32_t> h_res_stats;
         Pinned<int32_t> h_item_off, h_hitem_off, h_sub;
-        Pinned<BatchInfo> h_binfo; Pinned<int32_t> h_n;
+        Pinned<BatchInfo> h_binfo; Pinned<int32_t> h_n, h_own;
         Pinned<PoolMeta> h_meta;
     };
     // page-locked staging, kept across fits (cudaMallocHost is far too slow to repeat per call)
@@ -881,8 +879,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         DevBuf<NodeResult> d_res;
         DevBuf<int32_t> d_item_off, d_hitem_off, d_chunk_left, d_flist_all;
         DevBuf<uint32_t> d_lbits;                            // routing bits of the rows being partitioned
-        DevBuf<uint32_t> d_pack;                             // two 16-bit counters per word for the all-reduce of deep batches
-        size_t cap_pack = 0;
+        DevBuf<int32_t> d_own;                               // per batch: first node / accumulated rank of every rank's run
+        size_t cap_own = 0;
         size_t cap_nodes = 0, cap_hist = 0, cap_items = 0, cap_sub = 0, cap_lbits = 0;
         HistStore store;
         int64_t batch_stamp = 0;
@@ -911,13 +909,20 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     bool own_streams = num_sets > 1;
     if (const char* e = std::getenv("HAR_FIT_STREAMS")) own_streams = own_streams && std::atoi(e) > 1;
     // device-driven growth (all features per node), see further down
-    // Exchange of nodes with < 2^16 instances as two 16-bit counters per word: halves the all-reduced bytes (1.24 -> 0.66 GB
-    // per fit at 8 GPUs) but measured no faster at 2 or 8 GPUs (25.5 vs 25.45 ms: the collectives are hidden behind the
-    // other tree set or bound by rank skew, not bandwidth), so it is off unless HAR_PACK_EXCHANGE=1.
-    bool pack_exchange = false;
-    if (const char* e = std::getenv("HAR_PACK_EXCHANGE")) pack_exchange = std::atoi(e) != 0;
     bool device_grow = !subsample;
     if (const char* e = std::getenv("HAR_FIT_DEVICE_GROW")) device_grow = device_grow && std::atoi(e) != 0;
+    // Several ranks, the library's own NCCL communicator: the best-split scan is SHARED.  Every tree has an owner rank
+    // (contiguous blocks of each set's tree order); a batch's accumulated counters are summed onto the owners of their
+    // nodes (one ncclReduce per rank and batch instead of an all-reduce: half the bytes), the owner derives the
+    // siblings, scans its nodes, keeps their counters, and the 72-byte results + class counts are broadcast back.
+    // Same integers, same fp64 sequence per node, same tie order: the forest does not change.  HAR_SHARD_SCAN=0 or a
+    // callback transport keep the replicated scan behind an all-reduce.
+    bool shard_scan = device_grow && world > 1 && world <= MAX_OWNERS;
+    if (const char* e = std::getenv("HAR_SHARD_SCAN")) shard_scan = shard_scan && std::atoi(e) != 0;
+    if (shard_scan) shard_scan = dist_has_nccl(dist, s);      // collective decision, identical on every rank
+    const int my_rank = dist ? dist->rank : 0;
+    DevBuf<int32_t> d_owner;                                  // [T] owner rank of every tree
+    std::vector<int32_t> h_owner;
     const int64_t slot_words = (int64_t)full_len + C;
     int batch_cap = (int)std::min<int64_t>(1 << 20, std::max<int64_t>(2, budget_words / std::max<int64_t>(1, slot_words)));
     batch_cap &= ~1;                                                    // sibling pairs never straddle by parity alone
@@ -952,7 +957,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             const int64_t per_batch = std::min<int64_t>(batch_cap, lvl);
             S.cap_hist = (size_t)(per_batch * slot_words);
             HAR_CUDA(S.d_hist.alloc(S.cap_hist, s));
-            if (world > 1) { S.cap_pack = S.cap_hist / 2 + 1; HAR_CUDA(S.d_pack.alloc(S.cap_pack, s)); }
+            if (shard_scan) { S.cap_own = (size_t)nbl * 2 * (world + 1); HAR_CUDA(S.d_own.alloc(S.cap_own, s)); HAR_CUDA(S.pin->h_own.reserve(S.cap_own)); }
             S.cap_items = (size_t)(ceil_div(n * Ts, 256) + per_batch + 1);
             HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, s));
             S.cap_lbits = (size_t)((n * Ts + per_batch * 4096) / 32 + 1024);   // items x chunk_rows <= rows + nodes x chunk_rows
@@ -973,6 +978,17 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_CUDA(cudaEventCreateWithFlags(&sets[k].ev, cudaEventDisableTiming));
     }
     for (int t = 0; t < T; t++) sets[t % num_sets].stack.push_back({t, 0});
+    if (shard_scan) {
+        h_owner.assign(T, 0);
+        for (int k = 0; k < num_sets; k++) {
+            const int nr = (int)sets[k].my_trees.size();
+            for (int q = 0; q < nr; q++) h_owner[sets[k].my_trees[q]] = (int32_t)(((int64_t)q * world) / nr);
+        }
+        HAR_CUDA(d_owner.alloc(T, s));
+        HAR_CUDA(cudaMemcpyAsync(d_owner.p, h_owner.data(), sizeof(int32_t) * T, cudaMemcpyHostToDevice, s));
+        HAR_CUDA(cudaStreamSynchronize(s));                   // h_owner is read again only by the host
+    }
+    const int32_t* owner_p = shard_scan ? d_owner.p : nullptr;
     int64_t groups_run = 0;
 
     mark("buffers");
@@ -1134,7 +1150,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             if (int rc = dist_allreduce(dist, S.d_hist.p, (int64_t)reduce_words, S.st)) return rc;
             const unsigned copy_slices = (unsigned)std::max<int64_t>(1, std::min<int64_t>(8, full_len / 2048));
             if (n_derived > 0) {
-                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(S.d_nodes.p, C, S.d_hist.p, d_parent);
+                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(S.d_nodes.p, C, S.d_hist.p, d_parent, nullptr, 0);
                 HAR_LAUNCH_CHECK();
             }
             prof_begin(S.st);
@@ -1142,7 +1158,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             HAR_LAUNCH_CHECK();
             prof_end(PROF_BEST_SPLIT, S.st, (double)ng);
             if (subtract && !all_last_level) {
-                k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(S.d_nodes.p, S.d_res.p, C, S.d_hist.p, d_parent);
+                k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(S.d_nodes.p, S.d_res.p, C, S.d_hist.p, d_parent, nullptr, 0);
                 HAR_LAUNCH_CHECK();
             }
             if (!all_last_level && items > 0) {
@@ -1299,6 +1315,11 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             HAR_CUDA(S.d_binfo.alloc(S.cap_binfo, S.st));
             HAR_CUDA(S.pin->h_binfo.reserve(S.cap_binfo));
         }
+        if (shard_scan && (size_t)nb * 2 * (world + 1) > S.cap_own) {
+            S.cap_own = (size_t)nb * 4 * (world + 1);
+            HAR_CUDA(S.d_own.alloc(S.cap_own, S.st));
+            HAR_CUDA(S.pin->h_own.reserve(S.cap_own));
+        }
         return HAR_OK;
     };
     auto dd_ensure_kept = [&](FitSet& S, int which, int level_of_nodes, int64_t nodes_upper) -> int {
@@ -1312,6 +1333,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_CUDA(S.pin->h_n.reserve(2));
         HAR_CUDA(cudaMemcpyAsync(S.pin->h_binfo.p, S.d_binfo.p, sizeof(BatchInfo) * nb_upper, cudaMemcpyDeviceToHost, S.st));
         HAR_CUDA(cudaMemcpyAsync(S.pin->h_n.p, S.d_total.p + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, S.st));
+        if (shard_scan)
+            HAR_CUDA(cudaMemcpyAsync(S.pin->h_own.p, S.d_own.p, sizeof(int32_t) * nb_upper * 2 * (world + 1), cudaMemcpyDeviceToHost, S.st));
         HAR_CUDA(cudaEventRecord(S.ev, S.st));
         S.inflight = true;
         return HAR_OK;
@@ -1338,7 +1361,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_CUDA(cudaMemcpyAsync(S.d_total.p, S.pin->h_n.p + 1, sizeof(int32_t), cudaMemcpyHostToDevice, S.st));
         const int64_t nb = ceil_div(nr, batch_cap);
         k_grow_layout<<<(unsigned)nb, 256, 0, S.st>>>(S.lv_nodes[0].p, S.d_total.p, batch_cap, C, kNumSMs, S.lv_item_off[0].p,
-                                                     S.lv_hitem_off[0].p, S.d_binfo.p, S.d_total.p + 1);
+                                                     S.lv_hitem_off[0].p, S.d_binfo.p, S.d_total.p + 1, owner_p, world, S.d_own.p);
         HAR_LAUNCH_CHECK();
         t_prep += ms_since(t_a);
         return dd_fetch_info(S, nb);
@@ -1375,10 +1398,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             const int ng = bi.ng;
             if (ng <= 0) continue;
             fo->num_batches++;
-            if (trace) fprintf(stderr, "[har_forest_fit]   level %d batch %lld: %d nodes (%d derived, %d accumulated with 16-bit counters)\n", L, (long long)b, ng, bi.n_derived, bi.n_small);
-            const size_t wide_words = (size_t)bi.hb_direct + (size_t)ng * C;          // large nodes + class totals
-            const size_t small_words = (size_t)bi.n_small * full_len;
-            const size_t reduce_words = wide_words + small_words;
+            if (trace) fprintf(stderr, "[har_forest_fit]   level %d batch %lld: %d nodes (%d derived)\n", L, (long long)b, ng, bi.n_derived);
+            const size_t reduce_words = (size_t)bi.hb_direct + (size_t)ng * C;        // accumulated counters + class totals
             const size_t need_hist = reduce_words + (size_t)bi.n_derived * full_len;
             if (need_hist > S.cap_hist) { S.cap_hist = need_hist + need_hist / 4; HAR_CUDA(S.d_hist.alloc(S.cap_hist, S.st)); }
             if ((size_t)bi.items + 1 > S.cap_items) { S.cap_items = (size_t)bi.items * 2 + 1; HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, S.st)); }
@@ -1400,32 +1421,47 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 HAR_LAUNCH_CHECK();
                 prof_end(PROF_NODE_HIST, S.st, (double)bi.hist_rows);
             }
-            if (world > 1 && pack_exchange && small_words > 0) {
-                // nodes with < 2^16 weighted instances over all ranks: no counter reaches 2^16 on any rank or in the
-                // sum, so they are exchanged two per word; the large nodes and the class totals go as they are
-                if (int rc = dist_allreduce(dist, S.d_hist.p, (int64_t)wide_words, S.st)) return rc;
-                const int64_t pw = (int64_t)(small_words + 1) / 2;
-                if ((size_t)pw > S.cap_pack) { S.cap_pack = (size_t)pw + (size_t)pw / 4; HAR_CUDA(S.d_pack.alloc(S.cap_pack, S.st)); }
-                k_pack16<<<(unsigned)ceil_div(pw, 256), 256, 0, S.st>>>(S.d_hist.p + wide_words, (int64_t)small_words, S.d_pack.p);
-                HAR_LAUNCH_CHECK();
-                if (int rc = dist_allreduce(dist, S.d_pack.p, pw, S.st)) return rc;
-                k_unpack16<<<(unsigned)ceil_div(pw, 256), 256, 0, S.st>>>(S.d_pack.p, (int64_t)small_words, S.d_hist.p + wide_words);
-                HAR_LAUNCH_CHECK();
+            // the exchange (reduceByKey(_.merge(_))): counters onto the owners of their nodes, or an all-reduce
+            const int32_t* own = shard_scan ? S.pin->h_own.p + b * 2 * (world + 1) : nullptr;
+            int g_lo = 0, g_hi = ng;
+            if (shard_scan) {
+                int32_t* ptrs[2 * MAX_OWNERS]; int64_t cnts[2 * MAX_OWNERS]; int roots[2 * MAX_OWNERS];
+                for (int r = 0; r < world; r++) {
+                    ptrs[2 * r] = reinterpret_cast<int32_t*>(S.d_hist.p) + (int64_t)own[world + 1 + r] * full_len;
+                    cnts[2 * r] = (int64_t)(own[world + 1 + r + 1] - own[world + 1 + r]) * full_len;
+                    ptrs[2 * r + 1] = reinterpret_cast<int32_t*>(d_parent) + (int64_t)own[r] * C;
+                    cnts[2 * r + 1] = (int64_t)(own[r + 1] - own[r]) * C;
+                    roots[2 * r] = roots[2 * r + 1] = r;
+                }
+                if (int rc = dist_reduce_list(dist, 2 * world, ptrs, cnts, roots, S.st)) return rc;
+                g_lo = own[my_rank]; g_hi = own[my_rank + 1];
             } else if (int rc = dist_allreduce(dist, S.d_hist.p, (int64_t)reduce_words, S.st)) return rc;
             const unsigned copy_slices = (unsigned)std::max<int64_t>(1, std::min<int64_t>(8, full_len / 2048));
             if (bi.n_derived > 0) {
-                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(nodes, C, S.d_hist.p, d_parent);
+                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(nodes, C, S.d_hist.p, d_parent, owner_p, my_rank);
                 HAR_LAUNCH_CHECK();
             }
-            prof_begin(S.st);
-            k_best_split<<<ng, BS_THREADS, bs_smem, S.st>>>(nodes, ng, S.d_hist.p, d_parent, nullptr, loff_p, 0, fm, res, rstats);
-            HAR_LAUNCH_CHECK();
-            prof_end(PROF_BEST_SPLIT, S.st, (double)ng);
-            if (!last_level) {
-                if (subtract && S.kept_slots[cur] > 0) {
-                    k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(nodes, res, C, S.d_hist.p, d_parent);
-                    HAR_LAUNCH_CHECK();
+            if (g_hi > g_lo) {
+                prof_begin(S.st);
+                k_best_split<<<g_hi - g_lo, BS_THREADS, bs_smem, S.st>>>(nodes, ng, S.d_hist.p, d_parent, nullptr, loff_p, 0, fm, res, rstats, g_lo);
+                HAR_LAUNCH_CHECK();
+                prof_end(PROF_BEST_SPLIT, S.st, (double)(g_hi - g_lo));
+            }
+            if (!last_level && subtract && S.kept_slots[cur] > 0) {
+                // before the results travel: a rank keeps the counters of the nodes it owns, from its own results
+                k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(nodes, res, C, S.d_hist.p, d_parent, owner_p, my_rank);
+                HAR_LAUNCH_CHECK();
+            }
+            if (shard_scan) {
+                void* ptrs[2 * MAX_OWNERS]; int64_t bytes[2 * MAX_OWNERS]; int roots[2 * MAX_OWNERS];
+                for (int r = 0; r < world; r++) {
+                    ptrs[2 * r] = res + own[r]; bytes[2 * r] = (int64_t)(own[r + 1] - own[r]) * (int64_t)sizeof(NodeResult);
+                    ptrs[2 * r + 1] = rstats + (int64_t)own[r] * 3 * C; bytes[2 * r + 1] = (int64_t)(own[r + 1] - own[r]) * 3 * C * 4;
+                    roots[2 * r] = roots[2 * r + 1] = r;
                 }
+                if (int rc = dist_bcast_list(dist, 2 * world, ptrs, bytes, roots, S.st)) return rc;
+            }
+            if (!last_level) {
                 if (bi.items > 0) {
                     prof_begin(S.st);
                     k_part_count<<<(unsigned)bi.items, HIST_THREADS, 0, S.st>>>(nodes, io, ng, bi.chunk_rows, res, d_bins.p, ldb, n,
@@ -1460,7 +1496,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_LAUNCH_CHECK();
         const int64_t nb_next = ceil_div(next_upper, batch_cap);
         k_grow_layout<<<(unsigned)nb_next, 256, 0, S.st>>>(S.lv_nodes[nxt].p, S.d_total.p, batch_cap, C, kNumSMs, S.lv_item_off[nxt].p,
-                                                          S.lv_hitem_off[nxt].p, S.d_binfo.p, S.d_total.p + 1);
+                                                          S.lv_hitem_off[nxt].p, S.d_binfo.p, S.d_total.p + 1, owner_p, world, S.d_own.p);
         HAR_LAUNCH_CHECK();
         S.level = L + 1; S.cur = nxt;
         groups_run++;
