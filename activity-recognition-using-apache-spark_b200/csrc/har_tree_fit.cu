@@ -768,6 +768,17 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     if (ldb != F) HAR_CUDA(cudaMemsetAsync(d_bins.p, 0, (size_t)std::max<int64_t>(n, 1) * ldb, s));   // zero padding bytes
     if (int rc = bin_features_impl(d_X, n, F, ld, arity, fo->thresholds.data(), fo->nsplits.data(), MB, d_bins.p, ldb, s)) return rc;
 
+    // feature-major copy for the row partition (HAR_PART_COLUMNS=0: gather from the row-major table as before)
+    DevBuf<uint8_t> d_binsT;
+    const int64_t nT = (n + 31) & ~(int64_t)31;
+    {
+        static const bool off = [] { const char* e = std::getenv("HAR_PART_COLUMNS"); return e && std::atoi(e) == 0; }();
+        if (!off && n > 0 && p->max_depth > 0) {
+            HAR_CUDA(d_binsT.alloc((size_t)F * nT, s));
+            k_bins_transpose<<<dim3((unsigned)ceil_div(n, 32), (unsigned)ceil_div(F, 32)), 256, 0, s>>>(d_bins.p, n, F, ldb, d_binsT.p, nT);
+            HAR_LAUNCH_CHECK();
+        }
+    }
     mark("binned");
     HAR_CUDA(side.join(s));                              // weights are needed from here on
 
@@ -1164,7 +1175,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             if (!all_last_level && items > 0) {
                 prof_begin(S.st);
                 k_part_count<<<(unsigned)items, HIST_THREADS, 0, S.st>>>(S.d_nodes.p, S.d_item_off.p, ng, chunk_rows, S.d_res.p, d_bins.p, ldb, n,
-                                                                      perm0.p, perm1.p, S.d_chunk_left.p, S.d_lbits.p);
+                                                                      perm0.p, perm1.p, S.d_chunk_left.p, S.d_lbits.p, d_binsT.p, nT);
                 HAR_LAUNCH_CHECK();
                 prof_end(PROF_PART_COUNT, S.st, (double)rows_total);
                 k_part_scan<<<(unsigned)ceil_div(ng, 4), 128, 0, S.st>>>(S.d_item_off.p, ng, S.d_res.p, S.d_chunk_left.p);
@@ -1465,7 +1476,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 if (bi.items > 0) {
                     prof_begin(S.st);
                     k_part_count<<<(unsigned)bi.items, HIST_THREADS, 0, S.st>>>(nodes, io, ng, bi.chunk_rows, res, d_bins.p, ldb, n,
-                                                                               perm0.p, perm1.p, S.d_chunk_left.p, S.d_lbits.p);
+                                                                               perm0.p, perm1.p, S.d_chunk_left.p, S.d_lbits.p, d_binsT.p, nT);
                     HAR_LAUNCH_CHECK();
                     prof_end(PROF_PART_COUNT, S.st, (double)bi.rows_total);
                     k_part_scan<<<(unsigned)ceil_div(ng, 4), 128, 0, S.st>>>(io, ng, res, S.d_chunk_left.p);
