@@ -654,7 +654,18 @@ HAR_API int har_node_histogram(const uint8_t* d_bins, int64_t ldb, const uint8_t
     HAR_CUDA(cudaMemsetAsync(d_kind.p, KIND_CONT, F, s));
     const size_t smem = (HIST_TILE_WORDS + 32 + HIST_FTAB + HIST_FTAB / 16) * sizeof(uint32_t);
     const bool vec = (ldb % 16 == 0) && ((reinterpret_cast<uintptr_t>(d_bins) & 15) == 0);
-    if (vec) {
+    int max_width = 0;
+    for (int f = 0; f < F; f++) max_width = std::max(max_width, loff[f + 1] - loff[f]);
+    const int keys = (max_width + 7) & ~7;
+    bool lanes = F <= HISTL_MAX_FEATURES && keys <= HISTL_MAX_KEYS && nrows * ldb < (1LL << 32);
+    for (int f = 0; f < F && lanes; f++) lanes = (loff[f + 1] - loff[f]) % C == 0;
+    if (const char* e = std::getenv("HAR_HIST_LANES")) lanes = lanes && std::atoi(e) != 0;
+    if (lanes) {
+        const size_t sm = histl_smem_bytes(keys, F);
+        HAR_CUDA(cudaFuncSetAttribute(k_node_hist_lanes<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        k_node_hist_lanes<false><<<item_off[1], HIST_THREADS, sm, s>>>(d_nd.p, d_io.p, 1, chunk_rows, d_bins, (uint32_t)ldb, d_labels, d_weights,
+                                                                nrows, d_rows, nullptr, d_loff.p, d_kind.p, C, F, keys, 0, d_hist, d_parent);
+    } else if (vec) {
         HAR_CUDA(cudaFuncSetAttribute(k_node_hist<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_node_hist<false><<<item_off[1], HIST_THREADS, smem, s>>>(d_nd.p, d_io.p, 1, chunk_rows, d_bins, ldb, d_labels, d_weights,
                                                                   nrows, d_rows, nullptr, nullptr, d_loff.p, d_kind.p, C, d_hist, d_parent);
@@ -852,6 +863,18 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     const size_t hist_smem = (HIST_TILE_WORDS + 32 + HIST_FTAB + HIST_FTAB / 16) * sizeof(uint32_t);
     HAR_CUDA(cudaFuncSetAttribute(k_node_hist<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem));
     HAR_CUDA(cudaFuncSetAttribute(k_node_hist<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem));
+    // lane = feature histogram kernel: every node sees the same <= 48 features, few enough (bin, class) pairs per feature
+    // for two [key][32] tiles, and row * ldb fits 32 bits
+    int max_hbins = 0;
+    for (int f = 0; f < F; f++) max_hbins = std::max(max_hbins, (int)m.hist_bins[f]);
+    const int histl_keys = (max_hbins * C + 7) & ~7;
+    bool hist_lanes = !subsample && F <= HISTL_MAX_FEATURES && histl_keys <= HISTL_MAX_KEYS && (int64_t)n * ldb < (1LL << 32);
+    if (const char* e = std::getenv("HAR_HIST_LANES")) hist_lanes = hist_lanes && std::atoi(e) != 0;
+    const size_t histl_smem = histl_smem_bytes(histl_keys, F);
+    bool any_cat = false;
+    for (int f = 0; f < F; f++) any_cat = any_cat || m.kind[f] != KIND_CONT;
+    auto* hist_lanes_fn = any_cat ? k_node_hist_lanes<true> : k_node_hist_lanes<false>;
+    if (hist_lanes) HAR_CUDA(cudaFuncSetAttribute(hist_lanes_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)histl_smem));
     const size_t bs_smem = ((size_t)BS_ROWS * (C + 1) + 64 * C) * 4 * (BS_THREADS / 32) + MAX_CAT * (BS_THREADS / 32) * 12 + 128 +
                            sizeof(Cand) * (BS_THREADS / 32 + 1) + 64;
     HAR_CUDA(cudaFuncSetAttribute(k_best_split, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
@@ -1151,6 +1174,9 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 if (subsample)
                     k_node_hist<true><<<(unsigned)hitems, HIST_THREADS, hist_smem, S.st>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
                         d_lab.p, d_w, n, perm0.p, perm1.p, flist_p, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
+                else if (hist_lanes)
+                    hist_lanes_fn<<<(unsigned)hitems, HIST_THREADS, histl_smem, S.st>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, (uint32_t)ldb,
+                        d_lab.p, d_w, n, perm0.p, perm1.p, loff_p, d_kind.p, C, F, histl_keys, 1, S.d_hist.p, d_parent);
                 else
                     k_node_hist<false><<<(unsigned)hitems, HIST_THREADS, hist_smem, S.st>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
                         d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
@@ -1427,8 +1453,12 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             HAR_CUDA(cudaMemsetAsync(S.d_hist.p, 0, sizeof(uint32_t) * reduce_words, S.st));
             if (bi.hitems > 0) {
                 prof_begin(S.st);
-                k_node_hist<false><<<(unsigned)bi.hitems, HIST_THREADS, hist_smem, S.st>>>(nodes, ho, ng, bi.chunk_rows, d_bins.p, ldb,
-                    d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
+                if (hist_lanes)
+                    hist_lanes_fn<<<(unsigned)bi.hitems, HIST_THREADS, histl_smem, S.st>>>(nodes, ho, ng, bi.chunk_rows, d_bins.p, (uint32_t)ldb,
+                        d_lab.p, d_w, n, perm0.p, perm1.p, loff_p, d_kind.p, C, F, histl_keys, 1, S.d_hist.p, d_parent);
+                else
+                    k_node_hist<false><<<(unsigned)bi.hitems, HIST_THREADS, hist_smem, S.st>>>(nodes, ho, ng, bi.chunk_rows, d_bins.p, ldb,
+                        d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
                 HAR_LAUNCH_CHECK();
                 prof_end(PROF_NODE_HIST, S.st, (double)bi.hist_rows);
             }

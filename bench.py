@@ -56,6 +56,8 @@ def parse():
     ap.add_argument("--no-wisdm", action="store_true", help="skip the WISDM (configs 1-2) fit/transform timings")
     ap.add_argument("--no-config5", action="store_true", help="skip the 500-tree depth-12 predict sweep (config 5)")
     ap.add_argument("--config5-rows", type=int, default=100_000_000)
+    ap.add_argument("--no-config4", action="store_true", help="skip the 1e9-sample strong-scaling step (config 4)")
+    ap.add_argument("--config4-samples", type=int, default=1_000_000_000)
     return ap.parse_args()
 
 
@@ -290,10 +292,10 @@ def run_ours(args):
     if rank == 0:
         clocks.prepare()
 
-    def device_step(record=None):
+    def device_step(record=None, stream=None):
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
         ev[0].record()
-        feats, wu, wa, ws = feat.transform_device(user, act, ts, x, y, z)
+        feats, wu, wa, ws = feat.transform_device(*(stream if stream is not None else (user, act, ts, x, y, z)))
         ev[1].record()
         nw = feats.shape[0]
         labels = wa.to(torch.float64)
@@ -467,6 +469,38 @@ def run_ours(args):
         except Exception as e:
             config5 = {"error": repr(e)}
 
+    # ---- config 4: the same step over 1e9 samples split across the ranks (strong scaling), outside the timed region --
+    config4 = None
+    if not args.no_config4 and not args.strong:
+        n4 = args.config4_samples // world
+        s4 = synth.synth_stream(n4, first_sample=rank * n4, per_user=max(n4 // args.users, 1), seed=2018)
+        for _ in range(2):
+            f4, _, _ = device_step(stream=s4)
+        agree4 = ranks_agree(f4)
+        rec4 = []
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(3):
+            device_step(rec4, stream=s4)
+        c1.record()
+        barrier()
+        t4 = torch.tensor([c0.elapsed_time(c1) / 3], dtype=torch.float64, device="cuda")
+        if world > 1:
+            td.all_reduce(t4, op=td.ReduceOp.MAX)
+        ms4 = float(t4.item())
+        config4 = {"workload": "config 4: 1e9-sample stream row-sharded over the ranks (strong scaling), same forest settings",
+                   "global_samples": n4 * world, "samples_per_gpu": n4, "windows_per_gpu": rec4[-1][1], "steps": 3, "warmup": 2,
+                   "ms_per_step": ms4, "value": n4 * world / (ms4 * 1e-3), "unit": UNIT, "ranks_agree": agree4,
+                   "window_ms": sum(e[0][0].elapsed_time(e[0][1]) for e in rec4) / 3,
+                   "fit_ms": sum(e[0][1].elapsed_time(e[0][2]) for e in rec4) / 3,
+                   "predict_ms": sum(e[0][2].elapsed_time(e[0][3]) for e in rec4) / 3,
+                   "forest_nodes": rec4[-1][2], "timing": "CUDA events, max over ranks"}
+        if agree4 is False:
+            agree = False
+        del s4, f4, rec4
+        torch.cuda.empty_cache()
+
     if world > 1:
         from har_b200 import dist as hd
         barrier()
@@ -542,7 +576,7 @@ def run_ours(args):
                        "predict_ms": stage["predict_ms"], "windows_per_gpu": nw, "forest_nodes": rec[-1][2],
                        "node_groups": rec[-1][3].num_groups, "device_batches": rec[-1][4], "allreduce_calls": rec[-1][5][0], "allreduce_via": "library NCCL communicator" if rec[-1][5][2] else "caller's callback (torch.distributed)",
                        "allreduce_bytes": rec[-1][5][1], "train_accuracy": train_acc, "wisdm": wisdm},
-            "config5": config5,
+            "config4": config4, "config5": config5,
             "roofline": roofline, "window_stage_roofline": window_roof, "kernels": roofs,
             "step_ms": [starts[i].elapsed_time(marks[i + 1]) for i in range(args.steps)],
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk}

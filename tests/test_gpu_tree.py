@@ -58,7 +58,7 @@ def test_bag_weights_bit_exact(T, rate, po):
         assert np.array_equal(sub, o[:, po[1]:])
 
 
-@pytest.mark.parametrize("n,F,C", [(10000, 43, 6), (777, 5, 2), (4096, 130, 3)])
+@pytest.mark.parametrize("n,F,C", [(10000, 43, 6), (777, 5, 2), (4096, 130, 3), (5001, 33, 6), (6000, 48, 4), (3000, 32, 7), (2500, 47, 1)])
 def test_node_histogram_counts_exact(n, F, C):
     from har_b200 import core
     rng = np.random.RandomState(n)
