@@ -183,7 +183,7 @@ bool g_prof_on = false;
 std::vector<ProfPending> g_pending;
 std::vector<cudaEvent_t> g_free_events;
 struct ProfAcc { double ms = 0, units = 0; long long launches = 0; } g_acc[PROF_NUM];
-cudaEvent_t g_cur_start = nullptr;
+cudaEvent_t g_cur_start = nullptr, g_span_start = nullptr;
 cudaEvent_t take_event() {
     if (!g_free_events.empty()) { cudaEvent_t e = g_free_events.back(); g_free_events.pop_back(); return e; }
     cudaEvent_t e;
@@ -203,6 +203,18 @@ void prof_end(int id, cudaStream_t s, double units) {
     cudaEventRecord(b, s);
     g_pending.push_back({id, g_cur_start, b, units});
     g_cur_start = nullptr;
+}
+void prof_span_begin(cudaStream_t s) {
+    if (!g_prof_on) return;
+    g_span_start = take_event();
+    cudaEventRecord(g_span_start, s);
+}
+void prof_span_end(int id, cudaStream_t s, double units) {
+    if (!g_prof_on || !g_span_start) return;
+    cudaEvent_t b = take_event();
+    cudaEventRecord(b, s);
+    g_pending.push_back({id, g_span_start, b, units});
+    g_span_start = nullptr;
 }
 void prof_resolve() {
     for (auto& p : g_pending) {

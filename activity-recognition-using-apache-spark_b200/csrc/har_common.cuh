@@ -34,10 +34,13 @@ int dist_bcast_list(const har_dist* d, int n_ops, void* const* ptr, const int64_
 
 // optional CUDA-event timing of selected kernels (har_debug_profile_*; off by default)
 enum ProfId { PROF_NODE_HIST = 0, PROF_BEST_SPLIT, PROF_PART_COUNT, PROF_PART_SCATTER, PROF_WINDOW_FEATURES,
-              PROF_SEG_TILES, PROF_PREDICT, PROF_BIN, PROF_FIND_SPLITS, PROF_BAG, PROF_NUM };
+              PROF_SEG_TILES, PROF_PREDICT, PROF_BIN, PROF_FIND_SPLITS, PROF_BAG, PROF_WINDOW_SPAN, PROF_NUM };
 bool prof_enabled();
 void prof_begin(cudaStream_t s);
 void prof_end(int id, cudaStream_t s, double units);
+// a span over several launches (first kernel's start to last kernel's end, gaps included); may enclose prof_begin/prof_end pairs
+void prof_span_begin(cudaStream_t s);
+void prof_span_end(int id, cudaStream_t s, double units);
 void prof_resolve();
 
 #define HAR_CUDA(expr)                                                                         \

@@ -352,6 +352,7 @@ HAR_API int har_window_transform(const int32_t* d_user, const int32_t* d_activit
     int64_t* h_total = fused ? pinned_total() : nullptr;
     CountLane& lane = count_lane();
     const bool early = fused && h_total && lane.ensure() == cudaSuccess;
+    har::prof_span_begin(s);
     if (int rc = seg_launch(d_user, d_activity, d_ts, n, window_len, gap_ns, scratch.p, d_win_start, fused ? nullptr : d_win_user,
                             fused ? nullptr : d_win_activity, &d_total, s, early ? lane.scanned : nullptr)) return rc;
     if (fused) {
@@ -360,6 +361,7 @@ HAR_API int har_window_transform(const int32_t* d_user, const int32_t* d_activit
         if (cap > 0)
             if (int rc = features_launch(d_x, d_y, d_z, d_ts, n, d_win_start, cap, d_total, window_len, d_out, ld_out, s,
                                          d_user, d_activity, d_win_user, d_win_activity)) return rc;
+        har::prof_span_end(har::PROF_WINDOW_SPAN, s, (double)n);
         if (!early) return read_total(d_total, num_windows, s);
         // the count is ready as soon as the scan is: copy it on the side stream and wait for that copy only (the
         // feature kernel keeps running; `stream` must not free the scratch before it ends, hence the join below)

@@ -539,24 +539,26 @@ k_window_features_v4(const double* __restrict__ x, const double* __restrict__ y,
         const int hpos = hpair < 12 ? 2 * hpair + (int)((up >> (2 * hpair)) & 1u) : 24;
         const bool lane_top = lane_hi == hi && ((pk >> hpos) & 1u);
 
-        // ---- deviations and the 10-bin counts (5-bit fields of one double: exact below 2^53) ----
+        // ---- deviations and the bin counts.  Eleven 4-bit fields per accumulator (bin 10 = the samples equal to the
+        // maximum, folded into bin 9 at the end): an accumulator takes 13 samples at most, so no field overflows and the
+        // sum stays an exact integer below 2^44; no clamp per sample. ----
         double sq = 0.0, sq1 = 0.0, ab = 0.0, ab1 = 0.0, packed = 0.0, packed1 = 0.0;
 #pragma unroll
         for (int j = 0; j < W4_PER_LANE; j++) {
             const double d = v[j] - mean;
             const double q = __dmul_rn(v[j] - lo, scale);
-            const int bq = min(__double2loint(__dadd_rd(q, 4503599627370496.0)), 9);       // floor(q) for 0 <= q < 2^31
-            const double one = __hiloint2double((1023 + 5 * bq) << 20, 0);                 // 2^(5 * bin)
+            const int bq = __double2loint(__dadd_rd(q, 4503599627370496.0));               // floor(q), 0 <= q <= 10
+            const double one = __hiloint2double((1023 << 20) + (bq << 22), 0);             // 2^(4 * bin)
             if (j & 1) { sq1 = fma(d, d, sq1); ab1 += fabs(d); packed1 += one; }
             else { sq = fma(d, d, sq); ab += fabs(d); packed += one; }
         }
-        sq += sq1; ab += ab1; packed += packed1;
+        sq += sq1; ab += ab1;
         int npk = __popc(pk);
-        const unsigned long long pbits = (unsigned long long)__double2ll_rn(packed);
-        // ten 5-bit counts -> four words of 10-bit fields (bins 0,2,4 | 1,3,5 | 6,8 | 7,9): integer warp reductions
-        const unsigned F3 = 0x1fu | (0x1fu << 10) | (0x1fu << 20);
-        unsigned b024 = (unsigned)pbits & F3, b135 = (unsigned)(pbits >> 5) & F3;
-        unsigned b68 = (unsigned)(pbits >> 30) & F3, b79 = (unsigned)(pbits >> 35) & F3;
+        // 4-bit fields -> 8-bit fields (a window has 200 samples): even bins 0,2,4,6 | 8,10 and odd bins 1,3,5,7 | 9
+        const unsigned long long pa = (unsigned long long)__double2ll_rn(packed), pb = (unsigned long long)__double2ll_rn(packed1);
+        const unsigned long long M4 = 0x0f0f0f0f0f0f0f0full;
+        const unsigned long long ev = (pa & M4) + (pb & M4), od = ((pa >> 4) & M4) + ((pb >> 4) & M4);
+        unsigned e_lo = (unsigned)ev, e_hi = (unsigned)(ev >> 32), o_lo = (unsigned)od, o_hi = (unsigned)(od >> 32);
         int top_is_peak = lane_top ? 1 : 0;
 #pragma unroll
         for (int m = 4; m >= 1; m >>= 1) {
@@ -569,10 +571,10 @@ k_window_features_v4(const double* __restrict__ x, const double* __restrict__ y,
 #pragma unroll
         for (int m = 4; m >= 1; m >>= 1) {
             npk_top += __shfl_xor_sync(0xffffffffu, npk_top, m);
-            b024 += __shfl_xor_sync(0xffffffffu, b024, m);
-            b135 += __shfl_xor_sync(0xffffffffu, b135, m);
-            b68 += __shfl_xor_sync(0xffffffffu, b68, m);
-            b79 += __shfl_xor_sync(0xffffffffu, b79, m);
+            e_lo += __shfl_xor_sync(0xffffffffu, e_lo, m);
+            e_hi += __shfl_xor_sync(0xffffffffu, e_hi, m);
+            o_lo += __shfl_xor_sync(0xffffffffu, o_lo, m);
+            o_hi += __shfl_xor_sync(0xffffffffu, o_hi, m);
         }
         npk = (int)(npk_top & 0xffffu);
         top_is_peak = (npk_top >> 16) != 0;
@@ -624,11 +626,11 @@ k_window_features_v4(const double* __restrict__ x, const double* __restrict__ y,
                 const double a = (double)k, q = a * 0.005;
                 return fma(fma(-q, 200.0, a), 0.005, q);
             };
-            const unsigned w3 = (sub & 1) ? (sub < 6 ? b135 : b79) : (sub < 6 ? b024 : b68);
-            const int fld = sub < 6 ? (sub >> 1) : 0;                       // bins 6 and 7 are field 0 of their words
-            dstrow[a * 10 + sub] = frac200((w3 >> (10 * fld)) & 0x3ffu);
+            // lane `sub` writes bin `sub` (0..7): even bins sit in e_lo, odd ones in o_lo, byte sub / 2
+            dstrow[a * 10 + sub] = frac200((((sub & 1) ? o_lo : e_lo) >> (8 * (sub >> 1))) & 0xffu);
             if (sub < 2) {
-                dstrow[a * 10 + 8 + sub] = frac200(((sub ? b79 : b68) >> 10) & 0x3ffu);
+                // bin 8, and bin 9 with the samples equal to the maximum (field 10)
+                dstrow[a * 10 + 8 + sub] = frac200(sub ? (o_hi & 0xffu) + ((e_hi >> 8) & 0xffu) : (e_hi & 0xffu));
             } else if (sub == 2) {
                 dstrow[30 + a] = mean;
             } else if (sub == 3) {

@@ -111,7 +111,7 @@ def smem_atomic_peak(mode, words=8192):
 
 
 PROFILE_IDS = ("node_hist", "best_split", "part_count", "part_scatter", "window_features", "seg_tiles", "predict",
-               "bin_features", "find_splits", "bag_weights")
+               "bin_features", "find_splits", "bag_weights", "window_span")
 
 
 def profile(enable=None, reset=False):

@@ -247,7 +247,7 @@ class ClockSampler:
                     reasons.add(name)
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max((r[1] for r in self.rows), default=None),
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self._nvml is not None else "nvidia-smi",
-                "query_ms": getattr(self, "query_ms", []), "sampled": "between steps, inside the timed region"}
+                "query_ms": getattr(self, "query_ms", []), "sampled": "between fit and predict of every step (after the last step with several ranks), inside the timed region"}
 
 
 def measured_peaks():
@@ -292,8 +292,10 @@ def run_ours(args):
     if rank == 0:
         clocks.prepare()
 
-    def device_step(record=None, stream=None):
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    query_spans = []
+
+    def device_step(record=None, stream=None, sample=False):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
         ev[0].record()
         feats, wu, wa, ws = feat.transform_device(*(stream if stream is not None else (user, act, ts, x, y, z)))
         ev[1].record()
@@ -311,6 +313,19 @@ def run_ours(args):
                                  feature_subset="all", seed=2018, part_off=po, dist=dist)
         comm = core.comm_stats()
         ev[2].record()
+        if sample:
+            # NVML queries from a concurrent thread were seen to stall CUDA calls that create resources (one step of
+            # 260 ms instead of 22), so the clocks are read here, inside the timed region: the fit has just handed its
+            # forest to the host, so the GPU is idle either way, and it has not left its load state.  A query takes
+            # 1.5-70 ms of host time; that span is bracketed by its own events and subtracted from the timed total
+            # (reported in "clocks").  Placed here rather than between steps so that the next step's window stage is
+            # queued behind this step's predict, as in any loop over batches, instead of starting on an idle GPU.
+            qa, qb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            qa.record()
+            clocks.sample_now()
+            qb.record()
+            query_spans.append((qa, qb))
+        ev[4].record()
         raw, prob, pred = forest.predict(feats, is_forest=True)
         ev[3].record()
         if record is not None:
@@ -344,8 +359,6 @@ def run_ours(args):
     agree = ranks_agree(forest)
     core.profile(enable=True, reset=True)
     core.launch_count(reset=True)
-    if rank == 0:
-        pass                       # clocks are sampled inside the loop below
     rec = []
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -353,22 +366,16 @@ def run_ours(args):
     e0.record()
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     # with several ranks only after the last step: a query in the middle would make the other ranks wait for rank 0
-    sample_at = (set(range(args.steps)) if world == 1 else {args.steps - 1}) if rank == 0 else set()
-    query_spans = []
     for i in range(args.steps):
         starts[i].record()
-        device_step(rec)
+        device_step(rec, sample=(rank == 0 and world == 1))
         marks[i + 1].record()
-        if i in sample_at:
-            # NVML queries from a concurrent thread were seen to stall CUDA calls that create resources (one step of
-            # 260 ms instead of 22); the clocks are therefore read here, inside the timed region, right after a step
-            # (the GPU has not left its load state).  A query takes 1.5-70 ms of host time with the GPU idle; that
-            # span is bracketed by its own events and subtracted from the timed total (reported in "clocks").
-            qa, qb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            qa.record()
-            clocks.sample_now()
-            qb.record()
-            query_spans.append((qa, qb))
+    if rank == 0 and world > 1:
+        qa, qb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        qa.record()
+        clocks.sample_now()
+        qb.record()
+        query_spans.append((qa, qb))
     e1.record()
     barrier()
     launches = core.launch_count()
@@ -388,7 +395,7 @@ def run_ours(args):
     for ev, *_ in rec:
         stage["window_ms"] += ev[0].elapsed_time(ev[1]) / args.steps
         stage["fit_ms"] += ev[1].elapsed_time(ev[2]) / args.steps
-        stage["predict_ms"] += ev[2].elapsed_time(ev[3]) / args.steps
+        stage["predict_ms"] += ev[4].elapsed_time(ev[3]) / args.steps
     nw = rec[-1][1]
     value = n * world / (ms_step * 1e-3)
 
@@ -494,7 +501,7 @@ def run_ours(args):
                    "ms_per_step": ms4, "value": n4 * world / (ms4 * 1e-3), "unit": UNIT, "ranks_agree": agree4,
                    "window_ms": sum(e[0][0].elapsed_time(e[0][1]) for e in rec4) / 3,
                    "fit_ms": sum(e[0][1].elapsed_time(e[0][2]) for e in rec4) / 3,
-                   "predict_ms": sum(e[0][2].elapsed_time(e[0][3]) for e in rec4) / 3,
+                   "predict_ms": sum(e[0][4].elapsed_time(e[0][3]) for e in rec4) / 3,
                    "forest_nodes": rec4[-1][2], "timing": "CUDA events, max over ranks"}
         if agree4 is False:
             agree = False
@@ -533,6 +540,7 @@ def run_ours(args):
                        "runs on a side stream under split finding and binning",
         "best_split": "fp64 gini evaluation of every (feature, threshold) candidate (issue-bound), not HBM",
         "window_features": "issue/latency-bound (ncu: no pipe or memory unit above 60 %), see profiles/"}
+    span = kern.pop("window_span", None)       # a span over the window stage's launches, not a kernel
     dominant = max(kern, key=lambda k: kern[k]["ms_per_step"]) if kern else None
     roofs = {}
     for name, k in kern.items():
@@ -567,6 +575,12 @@ def run_ours(args):
     window_roof = {"bound": "hbm", "achieved": BYTES_PER_SAMPLE * n / (win_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                    "bytes_per_sample": BYTES_PER_SAMPLE, "stage_ms": win_ms}
     window_roof["frac"] = window_roof["achieved"] / peak
+    window_roof["stage_ms_is"] = ("CUDA events around the featurizer call of every timed step (host prologue of the call, "
+                                  "four launches and their gaps)")
+    if span:
+        # the same stage between the library's own events: first kernel's start to last kernel's end, gaps included
+        window_roof["device_span_ms"] = span["ms_per_step"]
+        window_roof["device_span_frac"] = BYTES_PER_SAMPLE * n / (span["ms_per_step"] * 1e-3) / 1e9 / peak
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.strong else "weak",
@@ -578,7 +592,8 @@ def run_ours(args):
                        "allreduce_bytes": rec[-1][5][1], "train_accuracy": train_acc, "wisdm": wisdm},
             "config4": config4, "config5": config5,
             "roofline": roofline, "window_stage_roofline": window_roof, "kernels": roofs,
-            "step_ms": [starts[i].elapsed_time(marks[i + 1]) for i in range(args.steps)],
+            "step_ms": [starts[i].elapsed_time(marks[i + 1]) - (query_spans[i][0].elapsed_time(query_spans[i][1]) if world == 1 else 0.0)
+                        for i in range(args.steps)],
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk}
     print(json.dumps(line))
     if world > 1:
