@@ -656,7 +656,7 @@ HAR_API int har_node_histogram(const uint8_t* d_bins, int64_t ldb, const uint8_t
     const bool vec = (ldb % 16 == 0) && ((reinterpret_cast<uintptr_t>(d_bins) & 15) == 0);
     int max_width = 0;
     for (int f = 0; f < F; f++) max_width = std::max(max_width, loff[f + 1] - loff[f]);
-    const int keys = (max_width + 7) & ~7;
+    const int keys = (max_width + 15) & ~15;
     bool lanes = F <= HISTL_MAX_FEATURES && keys <= HISTL_MAX_KEYS && nrows * ldb < (1LL << 32);
     for (int f = 0; f < F && lanes; f++) lanes = (loff[f + 1] - loff[f]) % C == 0;
     if (const char* e = std::getenv("HAR_HIST_LANES")) lanes = lanes && std::atoi(e) != 0;
@@ -867,10 +867,15 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     // for two [key][32] tiles, and row * ldb fits 32 bits
     int max_hbins = 0;
     for (int f = 0; f < F; f++) max_hbins = std::max(max_hbins, (int)m.hist_bins[f]);
-    const int histl_keys = (max_hbins * C + 7) & ~7;
+    const int histl_keys = (max_hbins * C + 15) & ~15;
     bool hist_lanes = !subsample && F <= HISTL_MAX_FEATURES && histl_keys <= HISTL_MAX_KEYS && (int64_t)n * ldb < (1LL << 32);
     if (const char* e = std::getenv("HAR_HIST_LANES")) hist_lanes = hist_lanes && std::atoi(e) != 0;
     const size_t histl_smem = histl_smem_bytes(histl_keys, F);
+    // packed exchange (two 16-bit counters per word) for batches of small nodes: needs every feature to start on an even counter
+    bool pack16_ok = hist_lanes;
+    for (int f = 0; f <= F; f++) pack16_ok = pack16_ok && (m.loff[f] % 2 == 0);
+    pack16_ok = pack16_ok && budget_words < (1LL << 31);      // exchange offsets are 32-bit
+    if (const char* e = std::getenv("HAR_PACK16")) pack16_ok = pack16_ok && std::atoi(e) != 0;
     bool any_cat = false;
     for (int f = 0; f < F; f++) any_cat = any_cat || m.kind[f] != KIND_CONT;
     auto* hist_lanes_fn = any_cat ? k_node_hist_lanes<true> : k_node_hist_lanes<false>;
@@ -909,6 +914,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         int cur_ng = 0;
         bool inflight = false, done = false;
         DevBuf<uint32_t> d_hist, d_res_stats;               // d_res_stats: [node][left | right | parent][C]
+        DevBuf<uint32_t> d_hist16;                          // packed counters of a batch of small nodes (multi-GPU exchange)
+        size_t cap_hist16 = 0;
         DevBuf<NodeDesc> d_nodes;
         DevBuf<NodeResult> d_res;
         DevBuf<int32_t> d_item_off, d_hitem_off, d_chunk_left, d_flist_all;
@@ -991,7 +998,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             const int64_t per_batch = std::min<int64_t>(batch_cap, lvl);
             S.cap_hist = (size_t)(per_batch * slot_words);
             HAR_CUDA(S.d_hist.alloc(S.cap_hist, s));
-            if (shard_scan) { S.cap_own = (size_t)nbl * 2 * (world + 1); HAR_CUDA(S.d_own.alloc(S.cap_own, s)); HAR_CUDA(S.pin->h_own.reserve(S.cap_own)); }
+            if (shard_scan) { S.cap_own = (size_t)nbl * 3 * (world + 1); HAR_CUDA(S.d_own.alloc(S.cap_own, s)); HAR_CUDA(S.pin->h_own.reserve(S.cap_own)); }
             S.cap_items = (size_t)(ceil_div(n * Ts, 256) + per_batch + 1);
             HAR_CUDA(S.d_chunk_left.alloc(S.cap_items, s));
             S.cap_lbits = (size_t)((n * Ts + per_batch * 4096) / 32 + 1024);   // items x chunk_rows <= rows + nodes x chunk_rows
@@ -1176,7 +1183,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                         d_lab.p, d_w, n, perm0.p, perm1.p, flist_p, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
                 else if (hist_lanes)
                     hist_lanes_fn<<<(unsigned)hitems, HIST_THREADS, histl_smem, S.st>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, (uint32_t)ldb,
-                        d_lab.p, d_w, n, perm0.p, perm1.p, loff_p, d_kind.p, C, F, histl_keys, 1, S.d_hist.p, d_parent);
+                        d_lab.p, d_w, n, perm0.p, perm1.p, loff_p, d_kind.p, C, F, histl_keys, 1, S.d_hist.p, d_parent, nullptr);
                 else
                     k_node_hist<false><<<(unsigned)hitems, HIST_THREADS, hist_smem, S.st>>>(S.d_nodes.p, S.d_hitem_off.p, ng, chunk_rows, d_bins.p, ldb,
                         d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
@@ -1352,7 +1359,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             HAR_CUDA(S.d_binfo.alloc(S.cap_binfo, S.st));
             HAR_CUDA(S.pin->h_binfo.reserve(S.cap_binfo));
         }
-        if (shard_scan && (size_t)nb * 2 * (world + 1) > S.cap_own) {
+        if (shard_scan && (size_t)nb * 3 * (world + 1) > S.cap_own) {
             S.cap_own = (size_t)nb * 4 * (world + 1);
             HAR_CUDA(S.d_own.alloc(S.cap_own, S.st));
             HAR_CUDA(S.pin->h_own.reserve(S.cap_own));
@@ -1371,7 +1378,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_CUDA(cudaMemcpyAsync(S.pin->h_binfo.p, S.d_binfo.p, sizeof(BatchInfo) * nb_upper, cudaMemcpyDeviceToHost, S.st));
         HAR_CUDA(cudaMemcpyAsync(S.pin->h_n.p, S.d_total.p + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, S.st));
         if (shard_scan)
-            HAR_CUDA(cudaMemcpyAsync(S.pin->h_own.p, S.d_own.p, sizeof(int32_t) * nb_upper * 2 * (world + 1), cudaMemcpyDeviceToHost, S.st));
+            HAR_CUDA(cudaMemcpyAsync(S.pin->h_own.p, S.d_own.p, sizeof(int32_t) * nb_upper * 3 * (world + 1), cudaMemcpyDeviceToHost, S.st));
         HAR_CUDA(cudaEventRecord(S.ev, S.st));
         S.inflight = true;
         return HAR_OK;
@@ -1398,7 +1405,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_CUDA(cudaMemcpyAsync(S.d_total.p, S.pin->h_n.p + 1, sizeof(int32_t), cudaMemcpyHostToDevice, S.st));
         const int64_t nb = ceil_div(nr, batch_cap);
         k_grow_layout<<<(unsigned)nb, 256, 0, S.st>>>(S.lv_nodes[0].p, S.d_total.p, batch_cap, C, kNumSMs, S.lv_item_off[0].p,
-                                                     S.lv_hitem_off[0].p, S.d_binfo.p, S.d_total.p + 1, owner_p, world, S.d_own.p);
+                                                     S.lv_hitem_off[0].p, S.d_binfo.p, S.d_total.p + 1, owner_p, world, S.d_own.p, 0);
         HAR_LAUNCH_CHECK();
         t_prep += ms_since(t_a);
         return dd_fetch_info(S, nb);
@@ -1450,12 +1457,21 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             NodeResult* res = S.pool_res.p + base + b * batch_cap;
             uint32_t* rstats = S.pool_stats.p + (base + b * batch_cap) * 3 * C;
             uint32_t* d_parent = S.d_hist.p + bi.hb_direct;
-            HAR_CUDA(cudaMemsetAsync(S.d_hist.p, 0, sizeof(uint32_t) * reduce_words, S.st));
+            const bool pack16 = shard_scan && pack16_ok && bi.small16 > 0;
+            if (pack16) {
+                const size_t need16 = (size_t)bi.xwords;
+                if (need16 > S.cap_hist16) { S.cap_hist16 = need16 + need16 / 4; HAR_CUDA(S.d_hist16.alloc(S.cap_hist16, S.st)); }
+                HAR_CUDA(cudaMemsetAsync(S.d_hist16.p, 0, sizeof(uint32_t) * need16, S.st));
+                HAR_CUDA(cudaMemsetAsync(d_parent, 0, sizeof(uint32_t) * (size_t)ng * C, S.st));
+            } else {
+                HAR_CUDA(cudaMemsetAsync(S.d_hist.p, 0, sizeof(uint32_t) * reduce_words, S.st));
+            }
             if (bi.hitems > 0) {
                 prof_begin(S.st);
                 if (hist_lanes)
                     hist_lanes_fn<<<(unsigned)bi.hitems, HIST_THREADS, histl_smem, S.st>>>(nodes, ho, ng, bi.chunk_rows, d_bins.p, (uint32_t)ldb,
-                        d_lab.p, d_w, n, perm0.p, perm1.p, loff_p, d_kind.p, C, F, histl_keys, 1, S.d_hist.p, d_parent);
+                        d_lab.p, d_w, n, perm0.p, perm1.p, loff_p, d_kind.p, C, F, histl_keys, 1, S.d_hist.p, d_parent,
+                        pack16 ? S.d_hist16.p : nullptr);
                 else
                     k_node_hist<false><<<(unsigned)bi.hitems, HIST_THREADS, hist_smem, S.st>>>(nodes, ho, ng, bi.chunk_rows, d_bins.p, ldb,
                         d_lab.p, d_w, n, perm0.p, perm1.p, nullptr, loff_p, d_kind.p, C, S.d_hist.p, d_parent);
@@ -1463,19 +1479,29 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 prof_end(PROF_NODE_HIST, S.st, (double)bi.hist_rows);
             }
             // the exchange (reduceByKey(_.merge(_))): counters onto the owners of their nodes, or an all-reduce
-            const int32_t* own = shard_scan ? S.pin->h_own.p + b * 2 * (world + 1) : nullptr;
+            const int32_t* own = shard_scan ? S.pin->h_own.p + b * 3 * (world + 1) : nullptr;
             int g_lo = 0, g_hi = ng;
             if (shard_scan) {
                 int32_t* ptrs[2 * MAX_OWNERS]; int64_t cnts[2 * MAX_OWNERS]; int roots[2 * MAX_OWNERS];
                 for (int r = 0; r < world; r++) {
-                    ptrs[2 * r] = reinterpret_cast<int32_t*>(S.d_hist.p) + (int64_t)own[world + 1 + r] * full_len;
-                    cnts[2 * r] = (int64_t)(own[world + 1 + r + 1] - own[world + 1 + r]) * full_len;
+                    if (pack16) {
+                        ptrs[2 * r] = reinterpret_cast<int32_t*>(S.d_hist16.p) + own[2 * (world + 1) + r];
+                        cnts[2 * r] = (int64_t)own[2 * (world + 1) + r + 1] - own[2 * (world + 1) + r];
+                    } else {
+                        ptrs[2 * r] = reinterpret_cast<int32_t*>(S.d_hist.p) + (int64_t)own[world + 1 + r] * full_len;
+                        cnts[2 * r] = (int64_t)(own[world + 1 + r + 1] - own[world + 1 + r]) * full_len;
+                    }
                     ptrs[2 * r + 1] = reinterpret_cast<int32_t*>(d_parent) + (int64_t)own[r] * C;
                     cnts[2 * r + 1] = (int64_t)(own[r + 1] - own[r]) * C;
                     roots[2 * r] = roots[2 * r + 1] = r;
                 }
                 if (int rc = dist_reduce_list(dist, 2 * world, ptrs, cnts, roots, S.st)) return rc;
                 g_lo = own[my_rank]; g_hi = own[my_rank + 1];
+                if (pack16 && g_hi > g_lo) {                        // the owned nodes' counters to their 32-bit places
+                    const unsigned sl = (unsigned)std::max<int64_t>(1, std::min<int64_t>(8, full_len / 2048));
+                    k_hist_unpack<<<dim3((unsigned)(g_hi - g_lo), sl), 256, 0, S.st>>>(nodes, g_lo, S.d_hist16.p, S.d_hist.p);
+                    HAR_LAUNCH_CHECK();
+                }
             } else if (int rc = dist_allreduce(dist, S.d_hist.p, (int64_t)reduce_words, S.st)) return rc;
             const unsigned copy_slices = (unsigned)std::max<int64_t>(1, std::min<int64_t>(8, full_len / 2048));
             if (bi.n_derived > 0) {
@@ -1537,7 +1563,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_LAUNCH_CHECK();
         const int64_t nb_next = ceil_div(next_upper, batch_cap);
         k_grow_layout<<<(unsigned)nb_next, 256, 0, S.st>>>(S.lv_nodes[nxt].p, S.d_total.p, batch_cap, C, kNumSMs, S.lv_item_off[nxt].p,
-                                                          S.lv_hitem_off[nxt].p, S.d_binfo.p, S.d_total.p + 1, owner_p, world, S.d_own.p);
+                                                          S.lv_hitem_off[nxt].p, S.d_binfo.p, S.d_total.p + 1, owner_p, world, S.d_own.p,
+                                                          (shard_scan && pack16_ok) ? 1 : 0);
         HAR_LAUNCH_CHECK();
         S.level = L + 1; S.cur = nxt;
         groups_run++;
