@@ -31,6 +31,8 @@ bool dist_has_nccl(const har_dist* d, cudaStream_t s);
 // node-sharded exchange (NCCL only): sums of int32 runs onto their owners / owners' byte runs to everybody, one group each
 int dist_reduce_list(const har_dist* d, int n_ops, int32_t* const* ptr, const int64_t* cnt, const int* root, cudaStream_t s);
 int dist_bcast_list(const har_dist* d, int n_ops, void* const* ptr, const int64_t* bytes, const int* root, cudaStream_t s);
+int dist_scatter_exchange(const har_dist* d, int32_t* xbuf, int64_t seg, int n_all, int32_t* const* all_ptr,
+                          const int64_t* all_cnt, cudaStream_t s);
 
 // optional CUDA-event timing of selected kernels (har_debug_profile_*; off by default)
 enum ProfId { PROF_NODE_HIST = 0, PROF_BEST_SPLIT, PROF_PART_COUNT, PROF_PART_SCATTER, PROF_WINDOW_FEATURES,

@@ -1030,6 +1030,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_CUDA(cudaStreamSynchronize(s));                   // h_owner is read again only by the host
     }
     const int32_t* owner_p = shard_scan ? d_owner.p : nullptr;
+    // exchange buffer (equal segments per rank, reduce-scatter): with the lane = feature histogram kernel only
+    const int xmode = (shard_scan && hist_lanes) ? (pack16_ok ? 2 : 1) : 0;
     int64_t groups_run = 0;
 
     mark("buffers");
@@ -1405,7 +1407,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         HAR_CUDA(cudaMemcpyAsync(S.d_total.p, S.pin->h_n.p + 1, sizeof(int32_t), cudaMemcpyHostToDevice, S.st));
         const int64_t nb = ceil_div(nr, batch_cap);
         k_grow_layout<<<(unsigned)nb, 256, 0, S.st>>>(S.lv_nodes[0].p, S.d_total.p, batch_cap, C, kNumSMs, S.lv_item_off[0].p,
-                                                     S.lv_hitem_off[0].p, S.d_binfo.p, S.d_total.p + 1, owner_p, world, S.d_own.p, 0);
+                                                     S.lv_hitem_off[0].p, S.d_binfo.p, S.d_total.p + 1, owner_p, world, S.d_own.p, xmode);
         HAR_LAUNCH_CHECK();
         t_prep += ms_since(t_a);
         return dd_fetch_info(S, nb);
@@ -1457,7 +1459,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             NodeResult* res = S.pool_res.p + base + b * batch_cap;
             uint32_t* rstats = S.pool_stats.p + (base + b * batch_cap) * 3 * C;
             uint32_t* d_parent = S.d_hist.p + bi.hb_direct;
-            const bool pack16 = shard_scan && pack16_ok && bi.small16 > 0;
+            const bool pack16 = xmode != 0;               // counters travel through the exchange buffer
             if (pack16) {
                 const size_t need16 = (size_t)bi.xwords;
                 if (need16 > S.cap_hist16) { S.cap_hist16 = need16 + need16 / 4; HAR_CUDA(S.d_hist16.alloc(S.cap_hist16, S.st)); }
@@ -1483,19 +1485,20 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             int g_lo = 0, g_hi = ng;
             if (shard_scan) {
                 int32_t* ptrs[2 * MAX_OWNERS]; int64_t cnts[2 * MAX_OWNERS]; int roots[2 * MAX_OWNERS];
-                for (int r = 0; r < world; r++) {
-                    if (pack16) {
-                        ptrs[2 * r] = reinterpret_cast<int32_t*>(S.d_hist16.p) + own[2 * (world + 1) + r];
-                        cnts[2 * r] = (int64_t)own[2 * (world + 1) + r + 1] - own[2 * (world + 1) + r];
-                    } else {
+                if (pack16) {
+                    int32_t* tot = reinterpret_cast<int32_t*>(d_parent);
+                    const int64_t tot_cnt = (int64_t)ng * C;
+                    if (int rc = dist_scatter_exchange(dist, reinterpret_cast<int32_t*>(S.d_hist16.p), bi.xseg, 1, &tot, &tot_cnt, S.st)) return rc;
+                } else {
+                    for (int r = 0; r < world; r++) {
                         ptrs[2 * r] = reinterpret_cast<int32_t*>(S.d_hist.p) + (int64_t)own[world + 1 + r] * full_len;
                         cnts[2 * r] = (int64_t)(own[world + 1 + r + 1] - own[world + 1 + r]) * full_len;
+                        ptrs[2 * r + 1] = reinterpret_cast<int32_t*>(d_parent) + (int64_t)own[r] * C;
+                        cnts[2 * r + 1] = (int64_t)(own[r + 1] - own[r]) * C;
+                        roots[2 * r] = roots[2 * r + 1] = r;
                     }
-                    ptrs[2 * r + 1] = reinterpret_cast<int32_t*>(d_parent) + (int64_t)own[r] * C;
-                    cnts[2 * r + 1] = (int64_t)(own[r + 1] - own[r]) * C;
-                    roots[2 * r] = roots[2 * r + 1] = r;
+                    if (int rc = dist_reduce_list(dist, 2 * world, ptrs, cnts, roots, S.st)) return rc;
                 }
-                if (int rc = dist_reduce_list(dist, 2 * world, ptrs, cnts, roots, S.st)) return rc;
                 g_lo = own[my_rank]; g_hi = own[my_rank + 1];
                 if (pack16 && g_hi > g_lo) {                        // the owned nodes' counters to their 32-bit places
                     const unsigned sl = (unsigned)std::max<int64_t>(1, std::min<int64_t>(8, full_len / 2048));
@@ -1507,6 +1510,11 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             if (bi.n_derived > 0) {
                 k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(nodes, C, S.d_hist.p, d_parent, owner_p, my_rank);
                 HAR_LAUNCH_CHECK();
+            }
+            if (shard_scan) {
+                // results travel as one sum over the ranks: every rank but the owner of a node contributes zero bits
+                HAR_CUDA(cudaMemsetAsync(res, 0, sizeof(NodeResult) * (size_t)ng, S.st));
+                HAR_CUDA(cudaMemsetAsync(rstats, 0, sizeof(uint32_t) * (size_t)ng * 3 * C, S.st));
             }
             if (g_hi > g_lo) {
                 prof_begin(S.st);
@@ -1520,13 +1528,10 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
                 HAR_LAUNCH_CHECK();
             }
             if (shard_scan) {
-                void* ptrs[2 * MAX_OWNERS]; int64_t bytes[2 * MAX_OWNERS]; int roots[2 * MAX_OWNERS];
-                for (int r = 0; r < world; r++) {
-                    ptrs[2 * r] = res + own[r]; bytes[2 * r] = (int64_t)(own[r + 1] - own[r]) * (int64_t)sizeof(NodeResult);
-                    ptrs[2 * r + 1] = rstats + (int64_t)own[r] * 3 * C; bytes[2 * r + 1] = (int64_t)(own[r + 1] - own[r]) * 3 * C * 4;
-                    roots[2 * r] = roots[2 * r + 1] = r;
-                }
-                if (int rc = dist_bcast_list(dist, 2 * world, ptrs, bytes, roots, S.st)) return rc;
+                static_assert(sizeof(NodeResult) % 4 == 0, "NodeResult travels as int32 words");
+                int32_t* ptrs[2] = {reinterpret_cast<int32_t*>(res), reinterpret_cast<int32_t*>(rstats)};
+                const int64_t cnts[2] = {(int64_t)ng * (int64_t)(sizeof(NodeResult) / 4), (int64_t)ng * 3 * C};
+                if (int rc = dist_scatter_exchange(dist, nullptr, 0, 2, ptrs, cnts, S.st)) return rc;
             }
             if (!last_level) {
                 if (bi.items > 0) {
@@ -1564,7 +1569,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
         const int64_t nb_next = ceil_div(next_upper, batch_cap);
         k_grow_layout<<<(unsigned)nb_next, 256, 0, S.st>>>(S.lv_nodes[nxt].p, S.d_total.p, batch_cap, C, kNumSMs, S.lv_item_off[nxt].p,
                                                           S.lv_hitem_off[nxt].p, S.d_binfo.p, S.d_total.p + 1, owner_p, world, S.d_own.p,
-                                                          (shard_scan && pack16_ok) ? 1 : 0);
+                                                          xmode);
         HAR_LAUNCH_CHECK();
         S.level = L + 1; S.cur = nxt;
         groups_run++;
