@@ -657,7 +657,7 @@ HAR_API int har_node_histogram(const uint8_t* d_bins, int64_t ldb, const uint8_t
     int max_width = 0;
     for (int f = 0; f < F; f++) max_width = std::max(max_width, loff[f + 1] - loff[f]);
     const int keys = (max_width + 15) & ~15;
-    bool lanes = F <= HISTL_MAX_FEATURES && keys <= HISTL_MAX_KEYS && nrows * ldb < (1LL << 32);
+    bool lanes = C <= 8 && F <= HISTL_MAX_FEATURES && keys <= HISTL_MAX_KEYS && nrows * ldb < (1LL << 32);
     for (int f = 0; f < F && lanes; f++) lanes = (loff[f + 1] - loff[f]) % C == 0;
     if (const char* e = std::getenv("HAR_HIST_LANES")) lanes = lanes && std::atoi(e) != 0;
     if (lanes) {
@@ -868,7 +868,7 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     int max_hbins = 0;
     for (int f = 0; f < F; f++) max_hbins = std::max(max_hbins, (int)m.hist_bins[f]);
     const int histl_keys = (max_hbins * C + 15) & ~15;
-    bool hist_lanes = !subsample && F <= HISTL_MAX_FEATURES && histl_keys <= HISTL_MAX_KEYS && (int64_t)n * ldb < (1LL << 32);
+    bool hist_lanes = !subsample && C <= 8 && F <= HISTL_MAX_FEATURES && histl_keys <= HISTL_MAX_KEYS && (int64_t)n * ldb < (1LL << 32);
     if (const char* e = std::getenv("HAR_HIST_LANES")) hist_lanes = hist_lanes && std::atoi(e) != 0;
     const size_t histl_smem = histl_smem_bytes(histl_keys, F);
     // packed exchange (two 16-bit counters per word) for batches of small nodes: needs every feature to start on an even counter
