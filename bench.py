@@ -535,10 +535,12 @@ def run_ours(args):
         "bag_weights": 1,                   # per (row, tree): one weight byte written
         "best_split": (F * 32 * 6 + 6) * 4 + 456}   # per node: its counters read once + one result record written
     limiter = {
-        "node_hist": "shared-memory atomics (red.shared.add.u32), not HBM",
+        "node_hist": "not HBM (bins are L2-resident): red.shared.add.u32 into a lane = feature tile that is conflict-free by "
+                     "construction; ncu (profiles/r02_summary.md): root level issue-bound (smsp__issue_active 75 %, LSU data pipe "
+                     "60 %), deep levels bound by per-work-item overhead (tile clear/flush)",
         "bag_weights": "one serial Well19937c stream per Spark partition (latency chain of the generator), not HBM; "
                        "runs on a side stream under split finding and binning",
-        "best_split": "fp64 gini evaluation of every (feature, threshold) candidate (issue-bound), not HBM",
+        "best_split": "fp64 gini evaluation of every (feature, threshold) candidate (issue-bound, ncu issue slots 66 %), not HBM",
         "window_features": "issue/latency-bound (ncu: no pipe or memory unit above 60 %), see profiles/"}
     span = kern.pop("window_span", None)       # a span over the window stage's launches, not a kernel
     dominant = max(kern, key=lambda k: kern[k]["ms_per_step"]) if kern else None
@@ -569,6 +571,7 @@ def run_ours(args):
             roofline["smem_atomic_peak_conflict_free_per_s"] = pk_free
             roofline["smem_atomic_peak_random_per_s"] = pk_rand
             roofline["smem_atomic_frac_of_random_peak"] = roofline["smem_atomics_per_s"] / pk_rand
+            roofline["smem_atomic_frac_of_conflict_free_peak"] = roofline["smem_atomics_per_s"] / pk_free
         except Exception as e:
             roofline["smem_atomic_peak_error"] = repr(e)
     win_ms = stage["window_ms"]
