@@ -28,6 +28,8 @@ struct har_forest {
     double* d_leaf = nullptr;     // [num_leaves][C]: DT = class counts, RF = counts / total
     int64_t* d_roots = nullptr;   // [T] index of each tree's root in d_nodes
     int leaf_mode = -1;           // is_forest flag the leaf table was built for
+    void* ev_pred = nullptr;      // cudaEvent_t recorded after the last predict: a mode switch on another stream waits for it
+                                  // before it rewrites the leaf vectors
     // Fits that grew the trees on the device (har_tree_fit.cu) write the tables above straight from the device-side
     // node pool; per-slot class counts stay on the device so the leaf table can be rebuilt for the other predict mode.
     // The flat host arrays are then filled on first use (har_forest_export / import paths) by `materialize`.

@@ -417,6 +417,9 @@ int build_device_tables(har_forest* f, int is_forest, cudaStream_t s) {
     int dev = 0;
     HAR_CUDA(cudaGetDevice(&dev));
     if (f->d_nodes && f->dev == dev && f->leaf_mode == is_forest) return HAR_OK;
+    // the leaf vectors are about to be rewritten (or freed): a predict of the other mode may still be reading them on
+    // another stream
+    if (f->ev_pred) HAR_CUDA(cudaStreamWaitEvent(s, (cudaEvent_t)f->ev_pred, 0));
     if (f->d_nodes && f->dev == dev && f->d_slot_stats) {
         // tables written by the fit on this device: only the leaf vectors depend on the predict mode
         har::pool_setup();
@@ -560,6 +563,12 @@ HAR_API int har_forest_predict(const har_forest_t* fc, const double* d_X, int64_
     }
     HAR_LAUNCH_CHECK();
     har::prof_end(har::PROF_PREDICT, s, (double)n);
+    if (!f->ev_pred) {
+        cudaEvent_t e = nullptr;
+        HAR_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        f->ev_pred = e;
+    }
+    HAR_CUDA(cudaEventRecord((cudaEvent_t)f->ev_pred, s));
     return HAR_OK;
 }
 
@@ -606,6 +615,7 @@ HAR_API int har_forest_import(int32_t T, int32_t C, int32_t F, const int64_t* tr
 
 HAR_API void har_forest_free(har_forest_t* f) {
     if (!f) return;
+    if (f->ev_pred) { cudaEventSynchronize((cudaEvent_t)f->ev_pred); cudaEventDestroy((cudaEvent_t)f->ev_pred); f->ev_pred = nullptr; }
     free_device_tables(f);
     delete f;
 }

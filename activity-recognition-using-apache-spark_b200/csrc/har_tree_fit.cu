@@ -961,6 +961,10 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     bool shard_scan = device_grow && world > 1 && world <= MAX_OWNERS;
     if (const char* e = std::getenv("HAR_SHARD_SCAN")) shard_scan = shard_scan && std::atoi(e) != 0;
     if (shard_scan) shard_scan = dist_has_nccl(dist, s);      // collective decision, identical on every rank
+    // tests: HAR_DEBUG_XBUF=1 takes the sharded path (owner table, exchange buffer with packed small nodes, unpack) with
+    // a single rank, where every exchange is the identity; that is how a one-GPU box covers this code
+    if (world == 1 && device_grow)
+        if (const char* e = std::getenv("HAR_DEBUG_XBUF")) shard_scan = std::atoi(e) != 0;
     const int my_rank = dist ? dist->rank : 0;
     DevBuf<int32_t> d_owner;                                  // [T] owner rank of every tree
     std::vector<int32_t> h_owner;

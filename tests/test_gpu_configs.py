@@ -83,6 +83,28 @@ def test_config3_shape_100_trees_depth_10_on_1e5_windows():
     _same_predictions(g, o, X[:20000])
 
 
+@pytest.mark.parametrize("pack16", ["1", "0"])
+def test_exchange_buffer_path_with_one_rank(monkeypatch, pack16):
+    """The multi-GPU data path (owner table, exchange buffer with small nodes packed to 16-bit pairs, unpack before the
+    split scan) taken by a single rank, where every exchange is the identity: the forest must not change.  Nodes of
+    the first levels hold more than 2^16 instances (plain words), deeper ones fewer (packed)."""
+    from har_b200 import core
+    n = 300_000
+    X, y, arity = synth_tree_data(n, F=43, C=6, seed=9)
+    P = 16
+    po = [(n * k) // P for k in range(P + 1)]
+    kw = dict(num_classes=6, num_trees=6, max_depth=7, max_bins=32, feature_subset="all", seed=11, part_off=po)
+    ref = core.fit_forest(X, y, **kw)
+    monkeypatch.setenv("HAR_DEBUG_XBUF", "1")
+    monkeypatch.setenv("HAR_PACK16", pack16)
+    g = core.fit_forest(X, y, **kw)
+    monkeypatch.delenv("HAR_DEBUG_XBUF")
+    for k in ("tree_off", "feature", "threshold", "left", "right", "stats", "gain"):
+        assert np.array_equal(np.asarray(getattr(ref, k)), np.asarray(getattr(g, k))), k
+    o = orc.fit_forest(X, y, **kw)
+    assert_forest_equal(o, g)
+
+
 def test_config5_predict_500_trees_depth_12_over_1e6_rows():
     from har_b200 import core
     X, y, arity = synth_tree_data(40000, F=43, C=6, seed=77)
