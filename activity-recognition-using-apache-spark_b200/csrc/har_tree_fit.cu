@@ -1036,6 +1036,9 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
     const int32_t* owner_p = shard_scan ? d_owner.p : nullptr;
     // exchange buffer (equal segments per rank, reduce-scatter): with the lane = feature histogram kernel only
     const int xmode = (shard_scan && hist_lanes) ? (pack16_ok ? 2 : 1) : 0;
+    // derived siblings are subtracted on the fly by the split scan and k_hist_save instead of being written out first
+    int fuse_derive = 1;
+    if (const char* e = std::getenv("HAR_FUSE_DERIVE")) fuse_derive = std::atoi(e) != 0;
     int64_t groups_run = 0;
 
     mark("buffers");
@@ -1512,7 +1515,8 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             } else if (int rc = dist_allreduce(dist, S.d_hist.p, (int64_t)reduce_words, S.st)) return rc;
             const unsigned copy_slices = (unsigned)std::max<int64_t>(1, std::min<int64_t>(8, full_len / 2048));
             if (bi.n_derived > 0) {
-                k_hist_derive<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(nodes, C, S.d_hist.p, d_parent, owner_p, my_rank);
+                k_hist_derive<<<dim3((unsigned)ng, fuse_derive ? 1u : copy_slices), fuse_derive ? 32 : 256, 0, S.st>>>(
+                    nodes, C, S.d_hist.p, d_parent, owner_p, my_rank, fuse_derive);
                 HAR_LAUNCH_CHECK();
             }
             if (shard_scan) {
@@ -1522,13 +1526,13 @@ HAR_API int har_forest_fit(const double* d_X, int64_t n, int32_t F, int64_t ld, 
             }
             if (g_hi > g_lo) {
                 prof_begin(S.st);
-                k_best_split<<<g_hi - g_lo, BS_THREADS, bs_smem, S.st>>>(nodes, ng, S.d_hist.p, d_parent, nullptr, loff_p, 0, fm, res, rstats, g_lo);
+                k_best_split<<<g_hi - g_lo, BS_THREADS, bs_smem, S.st>>>(nodes, ng, S.d_hist.p, d_parent, nullptr, loff_p, 0, fm, res, rstats, g_lo, fuse_derive);
                 HAR_LAUNCH_CHECK();
                 prof_end(PROF_BEST_SPLIT, S.st, (double)(g_hi - g_lo));
             }
             if (!last_level && subtract && S.kept_slots[cur] > 0) {
                 // before the results travel: a rank keeps the counters of the nodes it owns, from its own results
-                k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(nodes, res, C, S.d_hist.p, d_parent, owner_p, my_rank);
+                k_hist_save<<<dim3((unsigned)ng, copy_slices), 256, 0, S.st>>>(nodes, res, C, S.d_hist.p, d_parent, owner_p, my_rank, fuse_derive);
                 HAR_LAUNCH_CHECK();
             }
             if (shard_scan) {
